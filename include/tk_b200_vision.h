@@ -1,0 +1,187 @@
+/*
+ * tk_b200_vision.h — C-ABI of libtk_b200.so, the B200 (sm_100a) implementation
+ * of TrackieLLM's vision hot path.
+ *
+ * Part 1 keeps the reference's own entry points (name, signature, argument
+ * meaning, error behaviour); each cites the reference declaration it replaces.
+ * Part 2 is additive (batched / fused forms the reference has no equivalent
+ * of), same conventions: every call returns tk_error_code_t, TK_SUCCESS == 0,
+ * never aborts; kernel launchers are asynchronous on the given stream.
+ *
+ * There is NO CPU fallback behind any of these: without a CUDA device every
+ * compute entry point returns a TK_ERROR_GPU_* code.
+ */
+#ifndef TK_B200_VISION_H
+#define TK_B200_VISION_H
+
+#include "tk_b200_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ======================================================================== */
+/* Part 1 — reference entry points                                           */
+/* ======================================================================== */
+
+/* src/vision/tk_image_preprocessor.h:49-56.  HOST pointers in and out; the
+ * frame is uploaded, resized on the GPU with the reference CPU mapping
+ * (src/vision/tk_image_preprocessor.c:43-69), and the CHW fp32 tensor is
+ * downloaded; bit-identical to the reference's AVX build.  Unlike the
+ * reference it honours frame->stride (0 means tightly packed) and rejects
+ * width/height < 2 (the reference reads out of bounds there). */
+TK_NODISCARD tk_error_code_t tk_preprocessor_resize_and_normalize_to_chw(
+    const tk_video_frame_t* frame, float* out_tensor, uint32_t target_width,
+    uint32_t target_height, const float mean[3], const float std_dev[3]);
+
+/* src/gpu/cuda/tk_cuda_kernels.h:51.  DEVICE pointers inside params.  Uses the
+ * reference CPU mapping, not the half-pixel mapping of the reference CUDA
+ * kernel (src/gpu/cuda/tk_cuda_kernels.cu:133-158): the north star pins the
+ * CPU implementation.  Output fp32 CHW. */
+TK_NODISCARD tk_error_code_t tk_kernels_preprocess_image(const tk_preprocess_params_t* params, cudaStream_t stream);
+
+/* src/gpu/cuda/tk_cuda_kernels.h:64,78 */
+TK_NODISCARD tk_error_code_t tk_kernels_postprocess_depth_map(const tk_postprocess_depth_params_t* params, cudaStream_t stream);
+TK_NODISCARD tk_error_code_t tk_kernels_depth_to_point_cloud(const tk_depth_to_points_params_t* params, cudaStream_t stream);
+
+/* src/gpu/cuda/tk_cuda_kernels.h:92.  Any num_cols (the reference rejects
+ * > 1024 and is wrong for non-power-of-two, tk_cuda_kernels.cu:331-336,369). */
+TK_NODISCARD tk_error_code_t tk_kernels_softmax(const tk_softmax_params_t* params, cudaStream_t stream);
+
+/* src/gpu/cuda/tk_cuda_dispatch.h:72-171 */
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_create(tk_cuda_dispatcher_t** out_dispatcher, const tk_cuda_dispatcher_config_t* config);
+void tk_cuda_dispatch_destroy(tk_cuda_dispatcher_t** dispatcher);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_malloc(tk_cuda_dispatcher_t* dispatcher, tk_gpu_buffer_t* out_buffer, size_t size_bytes);
+void tk_cuda_dispatch_free(tk_cuda_dispatcher_t* dispatcher, tk_gpu_buffer_t* buffer);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_upload_async(tk_cuda_dispatcher_t* dispatcher, tk_gpu_buffer_t dst_buffer, const void* src_host_ptr, size_t size_bytes);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_download_async(tk_cuda_dispatcher_t* dispatcher, void* dst_host_ptr, tk_gpu_buffer_t src_buffer, size_t size_bytes);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_synchronize(tk_cuda_dispatcher_t* dispatcher);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_preprocess_image(tk_cuda_dispatcher_t* dispatcher, const tk_preprocess_params_t* params);
+TK_NODISCARD tk_error_code_t tk_cuda_dispatch_depth_to_point_cloud(tk_cuda_dispatcher_t* dispatcher, const tk_depth_to_points_params_t* params);
+
+/* src/gpu/extensions/cuda/tk_cuda_tensor_ops.h:513-522.  boxes: f32 [.., K, 4]
+ * as (x, y, w, h) top-left form, truncated to integer rects like
+ * src/vision/tk_object_detector.c:347-350; scores: f32 [K]; class-agnostic
+ * (no class tensor in this signature); indices: device i32[max_detections];
+ * num_detections: HOST pointer (the call synchronises). */
+TK_NODISCARD tk_error_code_t tk_cuda_tensor_nms(
+    tk_cuda_dispatcher_t* dispatcher, const tk_tensor_descriptor_t* boxes,
+    const tk_tensor_descriptor_t* scores, tk_gpu_buffer_t indices,
+    uint32_t* num_detections, uint32_t max_detections, float iou_threshold,
+    float score_threshold);
+
+/* src/vision/tk_attribute_classifier.h (tk_classify_dominant_color,
+ * tk_classify_door_state).  HOST frame; out string is malloc'd, caller frees. */
+TK_NODISCARD tk_error_code_t tk_classify_dominant_color(const tk_video_frame_t* frame, const tk_rect_t* bbox, char** out_color_name);
+TK_NODISCARD tk_error_code_t tk_classify_door_state(const tk_video_frame_t* frame, const tk_rect_t* bbox, char** out_state_name);
+
+/* src/vision/tk_object_detector.h:157 */
+void tk_object_detector_free_results(tk_detection_result_t** results);
+
+/* ======================================================================== */
+/* Part 2 — additive entry points                                            */
+/* ======================================================================== */
+
+typedef enum { TK_B200_OUT_F32 = 0, TK_B200_OUT_F16 = 1 } tk_b200_out_type_e;
+typedef enum { TK_B200_RESIZE_STRETCH = 0, TK_B200_RESIZE_LETTERBOX = 1 } tk_b200_resize_mode_e;
+/* EXACT: every fp32 operation of the reference in its order, no contraction;
+ *        bit-identical to the reference's AVX build.
+ * FAST : lerp form with FMA; within 1e-5 + 1e-5|ref| of the reference. */
+typedef enum { TK_B200_ARITH_EXACT = 0, TK_B200_ARITH_FAST = 1 } tk_b200_arith_e;
+typedef enum { TK_B200_ACT_RAW = 0, TK_B200_ACT_SIGMOID = 1, TK_B200_ACT_SOFTMAX = 2 } tk_b200_activation_e;
+
+/* Batched fused pre-process: N frames of one geometry -> [N][3][H][W]. */
+typedef struct {
+    const void*        d_input;                 /* frame 0 (device)                                  */
+    const void* const* d_input_ptrs;            /* optional DEVICE table of N frame pointers         */
+    uint64_t           input_frame_pitch_bytes; /* distance between frames when d_input_ptrs == NULL */
+    uint32_t           num_frames;
+    uint32_t           input_width;
+    uint32_t           input_height;
+    uint32_t           input_stride_bytes;      /* 0 = tightly packed                                */
+    tk_pixel_format_e  input_format;            /* RGB8, RGBA8 or I420                               */
+    void*              d_output;                /* device, fp32 or fp16, NCHW                        */
+    uint32_t           output_width;
+    uint32_t           output_height;
+    tk_b200_out_type_e output_type;
+    tk_b200_resize_mode_e resize_mode;
+    float              pad_value;               /* letterbox fill on the 0..255 scale                */
+    tk_b200_arith_e    arith;
+    TkFloat3           mean;
+    TkFloat3           std_dev;
+} tk_b200_preprocess_batch_params_t;
+
+TK_NODISCARD tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_batch_params_t* params, cudaStream_t stream);
+
+/* One decoded proposal / detection (28 bytes, packed ints and one float). */
+typedef struct {
+    int32_t   index;       /* proposal row inside its frame */
+    tk_rect_t bbox;
+    float     confidence;
+    uint32_t  class_id;
+} tk_b200_candidate_t;
+
+/* YOLO-head decode + threshold + ordered compaction
+ * (src/vision/tk_object_detector.c:343-355 completed). */
+typedef struct {
+    const float*         d_logits;          /* [N][P][5+C] fp32 row-major                         */
+    uint32_t             num_frames;
+    uint32_t             num_proposals;
+    uint32_t             num_classes;
+    float                confidence_threshold;
+    tk_b200_activation_e activation;
+    tk_b200_candidate_t* d_candidates;      /* [N][max_candidates], ascending proposal index      */
+    uint32_t*            d_counts;          /* [N] rows passing the threshold (may exceed the cap) */
+    uint32_t             max_candidates;
+} tk_b200_decode_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_params_t* params, cudaStream_t stream);
+
+/* Class-wise greedy IoU NMS over per-frame candidate lists. */
+typedef struct {
+    const tk_b200_candidate_t* d_candidates;   /* [N][max_candidates]                       */
+    const uint32_t*            d_counts;       /* [N]; min(count, max_candidates) are used   */
+    uint32_t                   num_frames;
+    uint32_t                   max_candidates;
+    float                      iou_threshold;
+    uint32_t                   max_detections;
+    int                        class_agnostic; /* 0 = only equal class_id suppresses         */
+    tk_b200_candidate_t*       d_detections;   /* [N][max_detections], (score desc, index asc) */
+    uint32_t*                  d_num_detections; /* [N]                                      */
+} tk_b200_nms_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* params, cudaStream_t stream);
+
+/* Row softmax with fused argmax (either output may be NULL). */
+typedef struct {
+    const float* d_input;       /* [rows][cols]           */
+    float*       d_softmax;     /* [rows][cols] or NULL   */
+    uint32_t*    d_argmax;      /* [rows] or NULL         */
+    uint32_t     num_rows;
+    uint32_t     num_cols;
+} tk_b200_argmax_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_argmax_rows(const tk_b200_argmax_params_t* params, cudaStream_t stream);
+
+/* Per-detection dominant colour (src/vision/tk_attribute_classifier.c:40-97)
+ * for M boxes of one device-resident RGB8 frame. */
+typedef struct {
+    const uint8_t*   d_frame;
+    uint32_t         width, height, stride_bytes;
+    const tk_rect_t* d_boxes;        /* [M]                              */
+    uint32_t         num_boxes;
+    uint32_t*        d_color_ids;    /* [M] index into tk_b200_color_name */
+    unsigned long long* d_bins;      /* [M][9] histogram or NULL          */
+} tk_b200_color_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_dominant_color(const tk_b200_color_params_t* params, cudaStream_t stream);
+const char* tk_b200_color_name(uint32_t color_id);
+
+/* Library self-description (no GPU needed). */
+const char* tk_b200_version(void);
+int tk_b200_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TK_B200_VISION_H */

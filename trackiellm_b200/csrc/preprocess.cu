@@ -1,0 +1,567 @@
+// preprocess.cu — fused frame ingest -> bilinear resize -> normalise -> NCHW pack.
+//
+// Replaces  tk_preprocessor_resize_and_normalize_to_chw
+//             (src/vision/tk_image_preprocessor.c:21-166, the parity target) and
+//           tk_cuda_preprocess_image_kernel / tk_kernels_preprocess_image
+//             (src/gpu/cuda/tk_cuda_kernels.cu:102-169, :252-303).
+//
+// B200 design (HBM-bound byte work, no tensor cores):
+//   * The global output-row space [0, N*H_out) is cut into one contiguous run
+//     per CTA (grid = resident CTAs), so every source row is fetched once per
+//     CTA and the load is balanced to +-1 row.
+//   * Source rows stream through a shared-memory ring filled by TMA 1-D bulk
+//     copies (cp.async.bulk + mbarrier complete_tx), issued by one thread, many
+//     rows ahead of the consumers; an unaligned source falls back to a
+//     cooperative byte copy into the same ring.
+//   * Each thread produces 4 consecutive output pixels x 3 channels from the
+//     ring (3 LDS.32 + funnel shift per source row and pixel, bank-conflict-free
+//     at the 1080p->640 ratio) and writes one 128-bit (fp32) or 64-bit (fp16)
+//     streaming store per channel plane.
+//   * EXACT arithmetic reproduces the reference's fp32 operation order with no
+//     contraction (bit-identical to its AVX build); the divide by std is the
+//     Markstein fma sequence on a host-computed correctly rounded reciprocal.
+#include "tk_common.cuh"
+
+namespace tkb {
+
+enum { FMT_RGB8 = 0, FMT_RGBA8 = 1, FMT_I420 = 2 };
+
+struct PreK {
+    const uint8_t* in_base;
+    const uint8_t* const* in_ptrs;
+    unsigned long long frame_pitch;
+    void* out;
+    uint32_t num_frames, src_w, src_h, src_stride, dst_w, dst_h;
+    uint32_t new_w, new_h, pad_left, pad_top;     // letterbox region inside dst (== dst for stretch)
+    float x_ratio, y_ratio;
+    float mean[3], stdv[3], rstd[3], fscale[3], fbias[3];
+    float pad_value;
+    uint32_t s_log2;        // ring slots = 1 << s_log2
+    uint32_t slot_bytes;    // bytes per ring slot (multiple of 16)
+    uint32_t copy_bytes;    // bytes per bulk copy of one (luma) row
+    uint32_t chroma_copy_bytes, chroma_pitch, chroma_h;
+    unsigned long long u_off, v_off;   // I420 plane offsets from the frame base
+    uint32_t u_slot_off, v_slot_off;   // I420 offsets inside a ring slot
+    uint32_t tab_w;         // dst_w rounded up to 4
+    uint32_t ring_off;      // byte offset of the ring in dynamic smem
+    uint32_t group_rows;    // output rows per consumer group
+    uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
+};
+
+static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
+
+__device__ __forceinline__ float magic_byte(uint32_t word, uint32_t sel) {
+    // PRMT: {byte sel of word, 0, 0, 0x4B} -> float 2^23 + byte
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | sel));
+}
+
+// Fetch the 2x2 source neighbourhood of one output pixel as biased floats
+// m[k][c] = 2^23 + value, k = {top-left, top-right, bottom-left, bottom-right}.
+template <int FMT>
+__device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, const uint8_t* row1,
+                                           int xb, float (&m)[4][3]) {
+    if constexpr (FMT == FMT_RGB8) {
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + (xb & ~3));
+        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + (xb & ~3));
+        uint32_t a0 = a[0], a1 = a[1], a2 = a[2];
+        uint32_t b0 = b[0], b1 = b[1], b2 = b[2];
+        uint32_t sh = (uint32_t)xb << 3;                 // funnel shift uses the low 5 bits
+        uint32_t alo = __funnelshift_r(a0, a1, sh), ahi = __funnelshift_r(a1, a2, sh);
+        uint32_t blo = __funnelshift_r(b0, b1, sh), bhi = __funnelshift_r(b1, b2, sh);
+        m[0][0] = magic_byte(alo, 0); m[0][1] = magic_byte(alo, 1); m[0][2] = magic_byte(alo, 2);
+        m[1][0] = magic_byte(alo, 3); m[1][1] = magic_byte(ahi, 0); m[1][2] = magic_byte(ahi, 1);
+        m[2][0] = magic_byte(blo, 0); m[2][1] = magic_byte(blo, 1); m[2][2] = magic_byte(blo, 2);
+        m[3][0] = magic_byte(blo, 3); m[3][1] = magic_byte(bhi, 0); m[3][2] = magic_byte(bhi, 1);
+    } else if constexpr (FMT == FMT_RGBA8) {
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + xb);
+        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + xb);
+        uint32_t a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            m[0][c] = magic_byte(a0, c); m[1][c] = magic_byte(a1, c);
+            m[2][c] = magic_byte(b0, c); m[3][c] = magic_byte(b1, c);
+        }
+    } else {
+        // I420: xb is the luma pixel index.  BT.601 full range, 16.16 fixed point,
+        // nearest chroma — the integer arithmetic of oracle_i420_to_rgb8.
+        const int cw = (int)(p.src_w >> 1);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint8_t* row = (k & 2) ? row1 : row0;
+            int x = xb + (k & 1);
+            int cx = min(x >> 1, cw - 1);
+            int yy = row[x];
+            int u = (int)row[p.u_slot_off + cx] - 128;
+            int v = (int)row[p.v_slot_off + cx] - 128;
+            int r = (yy * 65536 + 91881 * v + 32768) >> 16;
+            int g = (yy * 65536 - 22554 * u - 46802 * v + 32768) >> 16;
+            int b = (yy * 65536 + 116130 * u + 32768) >> 16;
+            r = min(max(r, 0), 255); g = min(max(g, 0), 255); b = min(max(b, 0), 255);
+            m[k][0] = __uint_as_float(0x4B000000u | (uint32_t)r);
+            m[k][1] = __uint_as_float(0x4B000000u | (uint32_t)g);
+            m[k][2] = __uint_as_float(0x4B000000u | (uint32_t)b);
+        }
+    }
+}
+
+// Reference arithmetic, src/vision/tk_image_preprocessor.c:63-66 then :84-98.
+template <bool EXACT>
+__device__ __forceinline__ float blend_norm(const PreK& p, int c, float m1, float m2, float m3, float m4,
+                                            float xd, float omx, float yd, float omy) {
+    if constexpr (EXACT) {
+        float p1 = __fsub_rn(m1, kBias), p2 = __fsub_rn(m2, kBias);
+        float p3 = __fsub_rn(m3, kBias), p4 = __fsub_rn(m4, kBias);
+        float t1 = __fmul_rn(__fmul_rn(p1, omx), omy);
+        float t2 = __fmul_rn(__fmul_rn(p2, xd), omy);
+        float t3 = __fmul_rn(__fmul_rn(p3, omx), yd);
+        float t4 = __fmul_rn(__fmul_rn(p4, xd), yd);
+        float v = __fadd_rn(__fadd_rn(__fadd_rn(t1, t2), t3), t4);
+        float t = __fsub_rn(__fmul_rn(v, 1.0f / 255.0f), p.mean[c]);
+        // correctly rounded t / std: q = t*y, r = t - q*std (exact), q' = q + r*y
+        float q = __fmul_rn(t, p.rstd[c]);
+        float r = __fmaf_rn(-q, p.stdv[c], t);
+        return __fmaf_rn(r, p.rstd[c], q);
+    } else {
+        float top = __fmaf_rn(xd, m2 - m1, m1 - kBias);
+        float bot = __fmaf_rn(xd, m4 - m3, m3 - kBias);
+        float v = __fmaf_rn(yd, bot - top, top);
+        return __fmaf_rn(v, p.fscale[c], p.fbias[c]);
+    }
+}
+
+template <bool EXACT>
+__device__ __forceinline__ float norm_only(const PreK& p, int c, float v) {
+    if constexpr (EXACT) {
+        float t = __fsub_rn(__fmul_rn(v, 1.0f / 255.0f), p.mean[c]);
+        float q = __fmul_rn(t, p.rstd[c]);
+        float r = __fmaf_rn(-q, p.stdv[c], t);
+        return __fmaf_rn(r, p.rstd[c], q);
+    } else {
+        return __fmaf_rn(v, p.fscale[c], p.fbias[c]);
+    }
+}
+
+// Inside-region output rows [a, b) of an item covering output rows [h0, h1).
+__device__ __forceinline__ void item_src_rows(const PreK& p, uint32_t h0, uint32_t h1, int& ylo, int& nrows) {
+    uint32_t a = max(h0, p.pad_top), b = min(h1, p.pad_top + p.new_h);
+    if (a >= b) { ylo = 0; nrows = 0; return; }
+    int y_first = __float2int_rz(__fmul_rn(p.y_ratio, (float)(a - p.pad_top)));
+    int y_last = __float2int_rz(__fmul_rn(p.y_ratio, (float)(b - 1 - p.pad_top)));
+    y_first = min(y_first, (int)p.src_h - 2);
+    y_last = min(y_last, (int)p.src_h - 2);
+    ylo = y_first;
+    nrows = y_last + 1 - y_first + 1;
+}
+
+template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
+__global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // 64 x 8 B
+    int* xb_tab = reinterpret_cast<int*>(smem + 512);
+    float* xd_tab = reinterpret_cast<float*>(smem + 512 + 4 * p.tab_w);
+    uint8_t* ring = smem + p.ring_off;
+
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    const int nthr = blockDim.x * blockDim.y;
+    const uint32_t S = 1u << p.s_log2, smask = S - 1;
+
+    if (TMA && tid == 0) {
+        for (uint32_t s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+        mbar_fence_init();
+    }
+    // Column table: byte offset of the left source pixel and x weight
+    // (src/vision/tk_image_preprocessor.c:48,50,52).
+    for (uint32_t w = tid; w < p.tab_w; w += nthr) {
+        uint32_t wc = min(w, p.dst_w - 1);
+        int xb = -1; float xd = 0.0f;
+        if (!LBOX || (wc - p.pad_left) < p.new_w) {
+            float gx = __fmul_rn(p.x_ratio, (float)(wc - p.pad_left));
+            int x = min(__float2int_rz(gx), (int)p.src_w - 2);
+            xd = __fsub_rn(gx, (float)x);
+            xb = (FMT == FMT_RGB8) ? 3 * x : (FMT == FMT_RGBA8 ? 4 * x : x);
+        }
+        xb_tab[w] = xb; xd_tab[w] = xd;
+    }
+    __syncthreads();
+
+    // This CTA's contiguous run of global output rows.
+    const unsigned long long total = (unsigned long long)p.num_frames * p.dst_h;
+    const unsigned long long g0 = total * blockIdx.x / gridDim.x;
+    const unsigned long long g1 = total * (blockIdx.x + 1) / gridDim.x;
+    if (g0 >= g1) return;
+    const uint32_t f_first = (uint32_t)(g0 / p.dst_h);
+    const uint32_t f_last = (uint32_t)((g1 - 1) / p.dst_h);
+
+    auto item_rows = [&](uint32_t f, uint32_t& h0, uint32_t& h1) {
+        h0 = (f == f_first) ? (uint32_t)(g0 - (unsigned long long)f_first * p.dst_h) : 0u;
+        unsigned long long end = g1 - (unsigned long long)f * p.dst_h;
+        h1 = end < p.dst_h ? (uint32_t)end : p.dst_h;
+    };
+    auto frame_ptr = [&](uint32_t f) -> const uint8_t* {
+        return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
+    };
+
+    // ---- producer cursor (uniform across threads; only tid 0 issues TMA) ----
+    uint32_t pf = f_first, p_seq = 0;
+    int p_row = 0, p_end = -1;           // next source row to stage, last row of the item
+    bool p_valid = false;
+    const uint8_t* p_base = nullptr;
+    auto producer_seek = [&]() {         // position on the next item that needs source rows
+        while (pf <= f_last) {
+            uint32_t h0, h1; item_rows(pf, h0, h1);
+            int ylo, n; item_src_rows(p, h0, h1, ylo, n);
+            if (n > 0) { p_row = ylo; p_end = ylo + n - 1; p_base = frame_ptr(pf); p_valid = true; return; }
+            ++pf;
+        }
+        p_valid = false;
+    };
+    producer_seek();
+
+    auto stage_row = [&](uint32_t seq, const uint8_t* base, int row) {
+        const uint32_t slot = seq & smask;
+        uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
+        const uint8_t* src = base + (size_t)row * p.src_stride;
+        if constexpr (TMA) {
+            if (tid == 0) {
+                if constexpr (FMT == FMT_I420) {
+                    uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+                    mbar_arrive_expect_tx(&bars[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
+                    bulk_g2s(dst, src, p.copy_bytes, &bars[slot]);
+                    bulk_g2s(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &bars[slot]);
+                    bulk_g2s(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &bars[slot]);
+                } else {
+                    mbar_arrive_expect_tx(&bars[slot], p.copy_bytes);
+                    bulk_g2s(dst, src, p.copy_bytes, &bars[slot]);
+                }
+            }
+        } else {
+            const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
+            for (uint32_t i = tid; i < nb; i += nthr) dst[i] = __ldg(src + i);
+            if constexpr (FMT == FMT_I420) {
+                uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+                const uint8_t* us = base + p.u_off + (size_t)cr * p.chroma_pitch;
+                const uint8_t* vs = base + p.v_off + (size_t)cr * p.chroma_pitch;
+                for (uint32_t i = tid; i < (p.src_w >> 1); i += nthr) {
+                    dst[p.u_slot_off + i] = __ldg(us + i);
+                    dst[p.v_slot_off + i] = __ldg(vs + i);
+                }
+            }
+        }
+    };
+    auto produce = [&](uint32_t limit_seq) {
+        if (TMA && tid == 0) fence_proxy_async();
+        while (p_valid && (int32_t)(p_seq - limit_seq) < 0) {
+            stage_row(p_seq, p_base, p_row);
+            ++p_seq;
+            if (++p_row > p_end) { ++pf; producer_seek(); }
+        }
+    };
+
+    // Pad rows/pixels (letterbox) carry the same normalisation as real pixels.
+    float padn[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) padn[c] = norm_only<EXACT>(p, c, p.pad_value);
+
+    const uint32_t Q = p.tab_w >> 2;
+    const size_t plane = (size_t)p.dst_w * p.dst_h;
+    uint32_t seq_base = 0;               // ring sequence number of the current item's first source row
+
+    for (uint32_t f = f_first; f <= f_last; ++f) {
+        uint32_t h0, h1; item_rows(f, h0, h1);
+        int ylo, nrows; item_src_rows(p, h0, h1, ylo, nrows);
+        for (uint32_t hg = h0; hg < h1; hg += p.group_rows) {
+            const uint32_t hge = min(hg + p.group_rows, h1);
+            // First source row this group still needs -> how far the producer may run.
+            uint32_t need_seq = seq_base;
+            {
+                uint32_t a = max(hg, p.pad_top), b = min(hge, p.pad_top + p.new_h);
+                if (a < b) {
+                    int y = min(__float2int_rz(__fmul_rn(p.y_ratio, (float)(a - p.pad_top))), (int)p.src_h - 2);
+                    need_seq = seq_base + (uint32_t)(y - ylo);
+                } else if (hg >= p.pad_top + p.new_h) {
+                    need_seq = seq_base + (uint32_t)nrows;
+                }
+            }
+            produce(need_seq + S);
+            if (!TMA) __syncthreads();
+
+            for (uint32_t h = hg + threadIdx.y; h < hge; h += blockDim.y) {
+                const bool vin = !LBOX || (h - p.pad_top) < p.new_h;
+                float yd = 0.0f, omy = 1.0f;
+                const uint8_t* row0 = ring;
+                const uint8_t* row1 = ring;
+                if (vin) {
+                    float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
+                    int y = min(__float2int_rz(gy), (int)p.src_h - 2);
+                    yd = __fsub_rn(gy, (float)y);
+                    omy = __fsub_rn(1.0f, yd);
+                    uint32_t q0 = seq_base + (uint32_t)(y - ylo), q1 = q0 + 1;
+                    row0 = ring + (size_t)(q0 & smask) * p.slot_bytes;
+                    row1 = ring + (size_t)(q1 & smask) * p.slot_bytes;
+                    if (TMA) {
+                        mbar_wait(&bars[q0 & smask], (q0 >> p.s_log2) & 1u);
+                        mbar_wait(&bars[q1 & smask], (q1 >> p.s_log2) & 1u);
+                    }
+                }
+                for (uint32_t q = threadIdx.x; q < Q; q += blockDim.x) {
+                    float o[3][4];
+                    if (vin) {
+                        const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+                        const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
+                        const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
+                        const float xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            if (LBOX && xbs[j] < 0) {
+                                o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2];
+                            } else {
+                                float m[4][3];
+                                fetch_quad<FMT>(p, row0, row1, xbs[j], m);
+                                const float xd = xds[j], omx = __fsub_rn(1.0f, xd);
+#pragma unroll
+                                for (int c = 0; c < 3; ++c)
+                                    o[c][j] = blend_norm<EXACT>(p, c, m[0][c], m[1][c], m[2][c], m[3][c], xd, omx, yd, omy);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
+                    }
+                    const size_t pix = (size_t)h * p.dst_w + 4u * q;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const size_t e = ((size_t)f * 3 + c) * plane + pix;
+                        if (p.vec_store) {
+                            if constexpr (F16) {
+                                __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
+                                __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
+                                uint2 v;
+                                v.x = *reinterpret_cast<uint32_t*>(&lo);
+                                v.y = *reinterpret_cast<uint32_t*>(&hi);
+                                __stcs(reinterpret_cast<uint2*>(static_cast<__half*>(p.out) + e), v);
+                            } else {
+                                __stcs(reinterpret_cast<float4*>(static_cast<float*>(p.out) + e),
+                                       make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                if (4u * q + j < p.dst_w) {
+                                    if constexpr (F16) static_cast<__half*>(p.out)[e + j] = __float2half_rn(o[c][j]);
+                                    else static_cast<float*>(p.out)[e + j] = o[c][j];
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();   // every reader is done with rows < next group's first row
+        }
+        seq_base += (uint32_t)nrows;
+    }
+}
+
+// ------------------------------------------------------------------------- //
+// Host side                                                                   //
+// ------------------------------------------------------------------------- //
+
+// Correctly rounded fp32 reciprocal (needed by the Markstein divide).
+static float rn_reciprocal(float s) {
+    float y = (float)(1.0 / (double)s);
+    float best = y;
+    double best_err = 1e300;
+    for (int d = -1; d <= 1; ++d) {
+        uint32_t b = tk_dm_float_to_bits(y) + (uint32_t)d;
+        float c = tk_dm_bits_to_float(b);
+        double err = 1.0 - (double)s * (double)c;      // exact product, exact near 1
+        if (err < 0) err = -err;
+        if (err < best_err) { best_err = err; best = c; }
+    }
+    return best;
+}
+
+void letterbox_geometry(uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh,
+                        uint32_t* nw, uint32_t* nh, uint32_t* pl, uint32_t* pt) {
+    unsigned long long a = (unsigned long long)dw * sh, b = (unsigned long long)dh * sw;
+    if (a <= b) {
+        *nw = dw;
+        unsigned long long v = (2ull * sh * dw + sw) / (2ull * sw);
+        *nh = (uint32_t)(v < 1 ? 1 : (v > dh ? dh : v));
+    } else {
+        *nh = dh;
+        unsigned long long v = (2ull * sw * dh + sh) / (2ull * sh);
+        *nw = (uint32_t)(v < 1 ? 1 : (v > dw ? dw : v));
+    }
+    *pl = (dw - *nw) / 2;
+    *pt = (dh - *nh) / 2;
+}
+
+template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
+static tk_error_code_t launch_variant(const PreK& k, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+    auto kern = preprocess_kernel<FMT, F16, EXACT, LBOX, TMA>;
+    TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    kern<<<grid, block, smem, stream>>>(k);
+    return launch_status("preprocess_kernel");
+}
+
+template <int FMT, bool F16, bool EXACT>
+static tk_error_code_t launch_fmt(const PreK& k, bool lbox, bool tma, dim3 g, dim3 b, size_t s, cudaStream_t st) {
+    if (lbox) return tma ? launch_variant<FMT, F16, EXACT, true, true>(k, g, b, s, st)
+                         : launch_variant<FMT, F16, EXACT, true, false>(k, g, b, s, st);
+    return tma ? launch_variant<FMT, F16, EXACT, false, true>(k, g, b, s, st)
+               : launch_variant<FMT, F16, EXACT, false, false>(k, g, b, s, st);
+}
+
+template <int FMT>
+static tk_error_code_t launch_type(const PreK& k, bool f16, bool exact, bool lbox, bool tma, dim3 g, dim3 b, size_t s, cudaStream_t st) {
+    if (f16) return exact ? launch_fmt<FMT, true, true>(k, lbox, tma, g, b, s, st)
+                          : launch_fmt<FMT, true, false>(k, lbox, tma, g, b, s, st);
+    return exact ? launch_fmt<FMT, false, true>(k, lbox, tma, g, b, s, st)
+                 : launch_fmt<FMT, false, false>(k, lbox, tma, g, b, s, st);
+}
+
+}  // namespace tkb
+
+using namespace tkb;
+
+extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_batch_params_t* prm, cudaStream_t stream) {
+    if (!prm || (!prm->d_input && !prm->d_input_ptrs) || !prm->d_output) return TK_ERROR_INVALID_ARGUMENT;
+    if (prm->num_frames == 0) return TK_SUCCESS;
+    if (prm->input_width == 0 || prm->input_height == 0 || prm->output_width == 0 || prm->output_height == 0)
+        return TK_ERROR_INVALID_DIMENSIONS;
+    // The reference mapping reads pixel x+1 / row y+1 (tk_image_preprocessor.c:59-61):
+    // undefined for a 1-pixel-wide or 1-row source, rejected here.
+    if (prm->input_width < 2 || prm->input_height < 2) return TK_ERROR_INVALID_DIMENSIONS;
+    for (int c = 0; c < 3; ++c) {
+        float s = (&prm->std_dev.x)[c];
+        if (!(s > 0.0f) || !(s < 3.0e38f)) return TK_ERROR_INVALID_ARGUMENT;
+    }
+    int fmt;
+    uint32_t bpp;
+    switch (prm->input_format) {
+        case TK_PIXEL_FORMAT_RGB8:  fmt = FMT_RGB8;  bpp = 3; break;
+        case TK_PIXEL_FORMAT_RGBA8: fmt = FMT_RGBA8; bpp = 4; break;
+        case TK_PIXEL_FORMAT_I420:  fmt = FMT_I420;  bpp = 1; break;
+        default: return TK_ERROR_INVALID_ARGUMENT;
+    }
+    const DeviceInfo* dev = device_info();
+    if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
+
+    PreK k{};
+    k.in_base = static_cast<const uint8_t*>(prm->d_input);
+    k.in_ptrs = reinterpret_cast<const uint8_t* const*>(prm->d_input_ptrs);
+    k.out = prm->d_output;
+    k.num_frames = prm->num_frames;
+    k.src_w = prm->input_width; k.src_h = prm->input_height;
+    const uint32_t row_bytes = prm->input_width * bpp;
+    k.src_stride = prm->input_stride_bytes ? prm->input_stride_bytes : row_bytes;
+    if (k.src_stride < row_bytes) return TK_ERROR_INVALID_ARGUMENT;
+    k.dst_w = prm->output_width; k.dst_h = prm->output_height;
+    k.new_w = k.dst_w; k.new_h = k.dst_h; k.pad_left = 0; k.pad_top = 0;
+    const bool lbox = prm->resize_mode == TK_B200_RESIZE_LETTERBOX;
+    if (lbox) letterbox_geometry(k.src_w, k.src_h, k.dst_w, k.dst_h, &k.new_w, &k.new_h, &k.pad_left, &k.pad_top);
+    // src/vision/tk_image_preprocessor.c:43-44 (uint -> float, fp32 divide)
+    k.x_ratio = ((float)k.src_w - 1.0f) / (float)k.new_w;
+    k.y_ratio = ((float)k.src_h - 1.0f) / (float)k.new_h;
+    for (int c = 0; c < 3; ++c) {
+        float mu = (&prm->mean.x)[c], sd = (&prm->std_dev.x)[c];
+        k.mean[c] = mu; k.stdv[c] = sd; k.rstd[c] = rn_reciprocal(sd);
+        k.fscale[c] = (float)(1.0 / (255.0 * (double)sd));
+        k.fbias[c] = (float)(-(double)mu / (double)sd);
+    }
+    k.pad_value = prm->pad_value;
+    unsigned long long frame_bytes = (unsigned long long)k.src_stride * k.src_h;
+    if (fmt == FMT_I420) {
+        if (k.src_w < 4 || k.src_h < 4) return TK_ERROR_INVALID_DIMENSIONS;
+        k.chroma_pitch = k.src_stride / 2;
+        k.chroma_h = k.src_h / 2;
+        k.u_off = (unsigned long long)k.src_stride * k.src_h;
+        k.v_off = k.u_off + (unsigned long long)k.chroma_pitch * k.chroma_h;
+        frame_bytes = k.v_off + (unsigned long long)k.chroma_pitch * k.chroma_h;
+    }
+    k.frame_pitch = prm->input_frame_pitch_bytes ? prm->input_frame_pitch_bytes : frame_bytes;
+
+    // Ring slot layout and the TMA eligibility test (16-byte rule of cp.async.bulk).
+    const uint32_t luma_slot = (row_bytes + 8 + 15) & ~15u;      // +8: the 3-word gather may overrun by <= 6 B
+    uint32_t slot = luma_slot;
+    if (fmt == FMT_I420) {
+        const uint32_t cbytes = ((k.src_w / 2) + 15) & ~15u;
+        k.u_slot_off = luma_slot; k.v_slot_off = luma_slot + cbytes;
+        slot = luma_slot + 2 * cbytes;
+        k.chroma_copy_bytes = cbytes;
+    }
+    k.slot_bytes = slot;
+    k.copy_bytes = (row_bytes + 15) & ~15u;
+    bool tma = !prm->d_input_ptrs && (reinterpret_cast<uintptr_t>(prm->d_input) % 16 == 0) &&
+               (k.frame_pitch % 16 == 0) && (k.src_stride % 16 == 0) && (k.copy_bytes <= k.src_stride);
+    if (fmt == FMT_I420)
+        tma = tma && (k.u_off % 16 == 0) && (k.v_off % 16 == 0) && (k.chroma_pitch % 16 == 0) &&
+              (k.chroma_copy_bytes <= k.chroma_pitch);
+
+    k.tab_w = (k.dst_w + 3) & ~3u;
+    k.ring_off = (512 + 8 * k.tab_w + 127) & ~127u;
+    k.vec_store = (k.dst_w % 4 == 0) && (reinterpret_cast<uintptr_t>(prm->d_output) % 16 == 0);
+
+    // Block shape: threads along x cover the row's pixel quads.
+    const uint32_t Q = k.tab_w / 4;
+    uint32_t tx = Q >= 160 ? 160 : ((Q + 31) & ~31u);
+    if (tx > 320) tx = 320;
+    uint32_t ty = 320 / tx; if (ty < 1) ty = 1;
+    dim3 block(tx, ty);
+
+    // Ring depth: largest power of two that fits the budget; two CTAs per SM when possible.
+    auto span_rows = [&](uint32_t g) { return (uint32_t)((double)(g - 1) * (double)k.y_ratio) + 3; };
+    uint32_t group = ty * 2;
+    size_t budget = 100 * 1024;
+    uint32_t s_log2 = 0;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        size_t avail = budget > k.ring_off ? budget - k.ring_off : 0;
+        uint32_t slots = (uint32_t)(avail / slot);
+        s_log2 = 0;
+        while ((2u << s_log2) <= slots && s_log2 < 6) ++s_log2;
+        if (slots >= 2 && (1u << s_log2) >= span_rows(group) + 1) break;
+        if (attempt == 0) { group = ty; }
+        else if (attempt == 1) { budget = (size_t)dev->max_smem_optin; group = ty * 2; }
+        else if (attempt == 2) { group = ty; }
+        else { tk_error_set_detail("source rows of %u bytes do not fit the shared-memory ring", slot); return TK_ERROR_NOT_IMPLEMENTED; }
+    }
+    k.s_log2 = s_log2;
+    k.group_rows = group;
+    const size_t smem = k.ring_off + ((size_t)slot << s_log2);
+
+    const unsigned long long total_rows = (unsigned long long)k.num_frames * k.dst_h;
+    unsigned long long max_ctas = (total_rows + group - 1) / group;
+    const uint32_t resident = (smem <= 110 * 1024 ? 2u : 1u) * (uint32_t)dev->sm_count;
+    dim3 grid((unsigned)(max_ctas < resident ? max_ctas : resident));
+
+    const bool f16 = prm->output_type == TK_B200_OUT_F16;
+    const bool exact = prm->arith == TK_B200_ARITH_EXACT;
+    switch (fmt) {
+        case FMT_RGB8:  return launch_type<FMT_RGB8>(k, f16, exact, lbox, tma, grid, block, smem, stream);
+        case FMT_RGBA8: return launch_type<FMT_RGBA8>(k, f16, exact, lbox, tma, grid, block, smem, stream);
+        default:        return launch_type<FMT_I420>(k, f16, exact, lbox, tma, grid, block, smem, stream);
+    }
+}
+
+// src/gpu/cuda/tk_cuda_kernels.cu:252-303 (validation order and codes kept).
+extern "C" tk_error_code_t tk_kernels_preprocess_image(const tk_preprocess_params_t* params, cudaStream_t stream) {
+    if (!params || !params->d_input_image || !params->d_output_tensor) return TK_ERROR_INVALID_ARGUMENT;
+    if (params->input_width == 0 || params->input_height == 0 || params->output_width == 0 || params->output_height == 0)
+        return TK_ERROR_INVALID_DIMENSIONS;
+    tk_b200_preprocess_batch_params_t b{};
+    b.d_input = params->d_input_image;
+    b.num_frames = 1;
+    b.input_width = params->input_width;
+    b.input_height = params->input_height;
+    b.input_stride_bytes = params->input_stride_bytes;
+    b.input_format = TK_PIXEL_FORMAT_RGB8;
+    b.d_output = params->d_output_tensor;
+    b.output_width = params->output_width;
+    b.output_height = params->output_height;
+    b.output_type = TK_B200_OUT_F32;
+    b.resize_mode = TK_B200_RESIZE_STRETCH;
+    b.arith = TK_B200_ARITH_EXACT;
+    b.mean = params->mean;
+    b.std_dev = params->std_dev;
+    return tk_b200_preprocess_batch(&b, stream);
+}

@@ -1,0 +1,79 @@
+// tk_common.cuh — shared host/device helpers for libtk_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/tk_b200_vision.h"
+#include "../../include/tk_b200_detmath.h"
+
+#define TK_CUDA_TRY(call, code)                                                     \
+    do {                                                                            \
+        cudaError_t e__ = (call);                                                   \
+        if (e__ != cudaSuccess) {                                                   \
+            tk_error_set_detail("%s:%d %s -> %s", __FILE__, __LINE__, #call,        \
+                                cudaGetErrorString(e__));                           \
+            return (code);                                                          \
+        }                                                                           \
+    } while (0)
+
+namespace tkb {
+
+struct DeviceInfo {
+    int sm_count;
+    int max_smem_optin;
+    int cc_major;
+};
+// Cached per-device properties; returns nullptr when no usable CUDA device.
+const DeviceInfo* device_info(int* out_device = nullptr);
+
+// Post-launch check shared by every launcher (reference convention:
+// cudaGetLastError after enqueue, src/gpu/cuda/tk_cuda_kernels.cu:297-300).
+inline tk_error_code_t launch_status(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        tk_error_set_detail("%s launch failed: %s", what, cudaGetErrorString(e));
+        return TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE;
+    }
+    return TK_SUCCESS;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t addr = smem_u32(bar), ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    } while (!ok);
+}
+// TMA 1-D bulk copy global -> shared, completion signalled on an mbarrier.
+// dst, src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+#endif
+
+}  // namespace tkb

@@ -1,0 +1,188 @@
+"""Host-side Python mirror of the reference's vision/GPU interface for the hot path.
+
+Every function here is a thin argument-marshalling layer over the C-ABI of
+libtk_b200.so (include/tk_b200_vision.h); torch is used only for device memory
+and streams.  Names follow the reference (`tk_kernels_preprocess_image`,
+`tk_preprocessor_resize_and_normalize_to_chw`, ...) with the `tk_` prefix
+dropped.  Nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _capi as capi
+from ._capi import (ACT_RAW, ACT_SIGMOID, ACT_SOFTMAX, ARITH_EXACT, ARITH_FAST, OUT_F16, OUT_F32,
+                    PIXEL_I420, PIXEL_RGB8, PIXEL_RGBA8, RESIZE_LETTERBOX, RESIZE_STRETCH)
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)   # src/vision/tk_object_detector.c:248
+IMAGENET_STD = (0.229, 0.224, 0.225)    # src/vision/tk_object_detector.c:249
+COLOR_NAMES = ("red", "yellow", "green", "cyan", "blue", "magenta", "black", "white", "gray")
+
+CAND_DTYPE = np.dtype([("index", "<i4"), ("x", "<i4"), ("y", "<i4"), ("w", "<i4"), ("h", "<i4"),
+                       ("confidence", "<f4"), ("class_id", "<u4")])
+CAND_WORDS = 7
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f3(v) -> capi.TkFloat3:
+    return capi.TkFloat3(float(v[0]), float(v[1]), float(v[2]))
+
+
+def _require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (there is no CPU path)")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+
+
+# --------------------------------------------------------------------------- #
+# (1) pre-processing                                                            #
+# --------------------------------------------------------------------------- #
+def preprocess_batch(frames: torch.Tensor, out_w: int, out_h: int, *, width: int | None = None,
+                     height: int | None = None, fmt: int = PIXEL_RGB8, stride: int = 0,
+                     out_dtype: torch.dtype = torch.float32, arith: int | None = None,
+                     resize: int = RESIZE_STRETCH, pad_value: float = 114.0,
+                     mean=IMAGENET_MEAN, std=IMAGENET_STD, out: torch.Tensor | None = None) -> torch.Tensor:
+    """tk_b200_preprocess_batch.  frames: u8 CUDA tensor, [N,H,W,3] (RGB8), [N,H,W,4] (RGBA8) or
+    [N, bytes] with width/height given (I420 or strided).  Returns [N,3,out_h,out_w]."""
+    _require_cuda(frames, "frames")
+    if frames.dtype != torch.uint8:
+        raise ValueError("frames must be uint8")
+    n = frames.shape[0]
+    if frames.dim() == 4:
+        height, width = frames.shape[1], frames.shape[2]
+    elif width is None or height is None:
+        raise ValueError("width/height required for flat frame buffers")
+    pitch = frames.stride(0) * frames.element_size()
+    f16 = out_dtype == torch.float16
+    if arith is None:
+        arith = ARITH_FAST if f16 else ARITH_EXACT
+    if out is None:
+        out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=frames.device)
+    p = capi.PreprocessBatchParams(
+        d_input=frames.data_ptr(), d_input_ptrs=None, input_frame_pitch_bytes=pitch, num_frames=n,
+        input_width=width, input_height=height, input_stride_bytes=stride, input_format=fmt,
+        d_output=out.data_ptr(), output_width=out_w, output_height=out_h,
+        output_type=OUT_F16 if f16 else OUT_F32, resize_mode=resize, pad_value=pad_value, arith=arith,
+        mean=_f3(mean), std_dev=_f3(std))
+    with torch.cuda.device(frames.device):
+        capi.check(capi.lib().tk_b200_preprocess_batch(C.byref(p), _stream()), "tk_b200_preprocess_batch")
+    return out
+
+
+def kernels_preprocess_image(frame: torch.Tensor, out_w: int, out_h: int, mean=IMAGENET_MEAN, std=IMAGENET_STD,
+                             stride: int = 0) -> torch.Tensor:
+    """tk_kernels_preprocess_image (reference signature, src/gpu/cuda/tk_cuda_kernels.h:51)."""
+    _require_cuda(frame, "frame")
+    h, w = frame.shape[0], frame.shape[1]
+    out = torch.empty((3, out_h, out_w), dtype=torch.float32, device=frame.device)
+    p = capi.PreprocessParams(frame.data_ptr(), w, h, stride or w * 3, out.data_ptr(), out_w, out_h, _f3(mean), _f3(std))
+    with torch.cuda.device(frame.device):
+        capi.check(capi.lib().tk_kernels_preprocess_image(C.byref(p), _stream()), "tk_kernels_preprocess_image")
+    return out
+
+
+def preprocessor_resize_and_normalize_to_chw(frame: np.ndarray, out_w: int, out_h: int,
+                                             mean=IMAGENET_MEAN, std=IMAGENET_STD) -> np.ndarray:
+    """tk_preprocessor_resize_and_normalize_to_chw (src/vision/tk_image_preprocessor.h:49-56):
+    HOST frame in, HOST fp32 CHW tensor out; the GPU does the work."""
+    frame = np.ascontiguousarray(frame, dtype=np.uint8)
+    h, w = frame.shape[:2]
+    vf = capi.VideoFrame(w, h, w * 3, PIXEL_RGB8, frame.ctypes.data)
+    out = np.empty((3, out_h, out_w), dtype=np.float32)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*std)
+    capi.check(capi.lib().tk_preprocessor_resize_and_normalize_to_chw(
+        C.byref(vf), out.ctypes.data_as(C.c_void_p), C.c_uint32(out_w), C.c_uint32(out_h), m, s),
+        "tk_preprocessor_resize_and_normalize_to_chw")
+    return out
+
+
+# --------------------------------------------------------------------------- #
+# (2)(3) decode + NMS                                                           #
+# --------------------------------------------------------------------------- #
+def decode_detections(logits: torch.Tensor, conf_thr: float, *, act: int = ACT_RAW, max_candidates: int = 4096,
+                      candidates: torch.Tensor | None = None, counts: torch.Tensor | None = None):
+    """tk_kernels_decode_detections.  logits [N,P,5+C] f32 CUDA ->
+    (candidates int32 [N,max_candidates,7] (view as CAND_DTYPE on host), counts u32-as-int32 [N])."""
+    _require_cuda(logits, "logits")
+    n, p, l = logits.shape
+    if candidates is None:
+        candidates = torch.empty((n, max_candidates, CAND_WORDS), dtype=torch.int32, device=logits.device)
+    if counts is None:
+        counts = torch.empty((n,), dtype=torch.int32, device=logits.device)
+    prm = capi.DecodeParams(logits.data_ptr(), n, p, l - 5, conf_thr, act, candidates.data_ptr(),
+                            counts.data_ptr(), max_candidates)
+    with torch.cuda.device(logits.device):
+        capi.check(capi.lib().tk_kernels_decode_detections(C.byref(prm), _stream()), "tk_kernels_decode_detections")
+    return candidates, counts
+
+
+def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float, max_detections: int, *,
+                  class_agnostic: bool = False, detections: torch.Tensor | None = None,
+                  num_detections: torch.Tensor | None = None):
+    """tk_kernels_nms_classwise -> (detections int32 [N,max_detections,7], num_detections int32 [N])."""
+    _require_cuda(candidates, "candidates")
+    n, cap = candidates.shape[0], candidates.shape[1]
+    if detections is None:
+        detections = torch.empty((n, max_detections, CAND_WORDS), dtype=torch.int32, device=candidates.device)
+    if num_detections is None:
+        num_detections = torch.empty((n,), dtype=torch.int32, device=candidates.device)
+    prm = capi.NmsParams(candidates.data_ptr(), counts.data_ptr(), n, cap, iou_thr, max_detections,
+                         int(class_agnostic), detections.data_ptr(), num_detections.data_ptr())
+    with torch.cuda.device(candidates.device):
+        capi.check(capi.lib().tk_kernels_nms_classwise(C.byref(prm), _stream()), "tk_kernels_nms_classwise")
+    return detections, num_detections
+
+
+def candidates_to_numpy(cands: torch.Tensor, counts: torch.Tensor) -> list[np.ndarray]:
+    """Device candidate/detection lists -> per-frame structured host arrays."""
+    c = cands.cpu().numpy()
+    k = counts.cpu().numpy()
+    cap = c.shape[1]
+    return [np.ascontiguousarray(c[i, :min(int(k[i]), cap)]).view(CAND_DTYPE).reshape(-1) for i in range(c.shape[0])]
+
+
+# --------------------------------------------------------------------------- #
+# (4) softmax / argmax / dominant colour                                        #
+# --------------------------------------------------------------------------- #
+def kernels_softmax(x: torch.Tensor) -> torch.Tensor:
+    """tk_kernels_softmax (src/gpu/cuda/tk_cuda_kernels.h:92)."""
+    _require_cuda(x, "x")
+    out = torch.empty_like(x)
+    p = capi.SoftmaxParams(x.data_ptr(), out.data_ptr(), x.shape[0], x.shape[1])
+    with torch.cuda.device(x.device):
+        capi.check(capi.lib().tk_kernels_softmax(C.byref(p), _stream()), "tk_kernels_softmax")
+    return out
+
+
+def argmax_rows(x: torch.Tensor, want_softmax: bool = True):
+    """tk_kernels_argmax_rows -> (softmax or None, argmax int32 [rows])."""
+    _require_cuda(x, "x")
+    sm = torch.empty_like(x) if want_softmax else None
+    am = torch.empty((x.shape[0],), dtype=torch.int32, device=x.device)
+    p = capi.ArgmaxParams(x.data_ptr(), sm.data_ptr() if sm is not None else None, am.data_ptr(), x.shape[0], x.shape[1])
+    with torch.cuda.device(x.device):
+        capi.check(capi.lib().tk_kernels_argmax_rows(C.byref(p), _stream()), "tk_kernels_argmax_rows")
+    return sm, am
+
+
+def dominant_color(frame: torch.Tensor, boxes: torch.Tensor, want_bins: bool = False):
+    """tk_kernels_dominant_color.  frame [H,W,3] u8 CUDA, boxes int32 [M,4] (x,y,w,h) CUDA."""
+    _require_cuda(frame, "frame")
+    _require_cuda(boxes, "boxes")
+    h, w = frame.shape[0], frame.shape[1]
+    m = boxes.shape[0]
+    ids = torch.empty((m,), dtype=torch.int32, device=frame.device)
+    bins = torch.empty((m, 9), dtype=torch.int64, device=frame.device) if want_bins else None
+    p = capi.ColorParams(frame.data_ptr(), w, h, w * 3, boxes.data_ptr(), m, ids.data_ptr(),
+                         bins.data_ptr() if bins is not None else None)
+    with torch.cuda.device(frame.device):
+        capi.check(capi.lib().tk_kernels_dominant_color(C.byref(p), _stream()), "tk_kernels_dominant_color")
+    return ids, bins
