@@ -177,6 +177,30 @@ typedef struct {
 TK_NODISCARD tk_error_code_t tk_kernels_dominant_color(const tk_b200_color_params_t* params, cudaStream_t stream);
 const char* tk_b200_color_name(uint32_t color_id);
 
+/* Per-detection door state (src/vision/tk_attribute_classifier.c:100-157):
+ * strong-vertical-edge density of the box interior; state 1 = "closed". */
+typedef struct {
+    const uint8_t*   d_frame;
+    uint32_t         width, height, stride_bytes;
+    const tk_rect_t* d_boxes;        /* [M]              */
+    uint32_t         num_boxes;
+    uint32_t*        d_states;       /* [M] 1 = closed   */
+    int32_t*         d_edge_pixels;  /* [M] or NULL      */
+} tk_b200_door_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_door_state(const tk_b200_door_params_t* params, cudaStream_t stream);
+
+/* Handle accessors, so tk_kernels_* launchers can run on a dispatcher's buffers
+ * and compute stream. */
+void*        tk_b200_buffer_device_ptr(tk_gpu_buffer_t buffer);
+size_t       tk_b200_buffer_size(tk_gpu_buffer_t buffer);
+cudaStream_t tk_b200_dispatch_stream(tk_cuda_dispatcher_t* dispatcher);
+int          tk_b200_dispatch_device(tk_cuda_dispatcher_t* dispatcher);
+
+/* Pinned (page-locked, portable) host memory for the host-buffer entry points. */
+TK_NODISCARD tk_error_code_t tk_b200_host_alloc(void** out_ptr, size_t size_bytes);
+void tk_b200_host_free(void* ptr);
+
 /* Library self-description (no GPU needed). */
 const char* tk_b200_version(void);
 int tk_b200_device_count(void);

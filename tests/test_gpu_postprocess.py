@@ -1,0 +1,138 @@
+"""GPU parity: decode + ordered compaction, class-wise NMS, tk_cuda_tensor_nms — bit-exact vs the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import oracle as O
+from trackiellm_b200 import vision as V
+
+pytestmark = pytest.mark.gpu
+
+
+def same(a, b):
+    return a.shape == b.shape and a.tobytes() == b.tobytes()
+
+
+def gpu_decode(t, thr, act=V.ACT_RAW, cap=4096):
+    d = torch.from_numpy(np.ascontiguousarray(t)).cuda()
+    if d.dim() == 2:
+        d = d[None]
+    c, n = V.decode_detections(d, thr, act=act, max_candidates=cap)
+    torch.cuda.synchronize()
+    return c, n
+
+
+@pytest.mark.parametrize("act", [V.ACT_RAW, V.ACT_SIGMOID, V.ACT_SOFTMAX])
+@pytest.mark.parametrize("seed,adv", [(0, True), (1, False), (2, True)])
+def test_decode_bitexact(act, seed, adv):
+    t = synth.logits_tensor(seed, adversarial=adv, as_logit=(act != V.ACT_RAW))
+    c, n = gpu_decode(t, 0.5, act)
+    ref, total = O.decode(t, 0.5, act)
+    got = V.candidates_to_numpy(c, n)[0]
+    assert int(n[0]) == total
+    assert same(got, ref.view(V.CAND_DTYPE))
+
+
+@pytest.mark.parametrize("P,C", [(1, 80), (31, 80), (257, 3), (1000, 1), (25200, 0), (8 * 32 * 5 + 1, 80), (5000, 300)])
+def test_decode_ragged_shapes(P, C):
+    t = synth.logits_tensor(3, num_proposals=P, num_classes=C, objects=5, dups=3)
+    for act in (V.ACT_RAW, V.ACT_SOFTMAX):
+        c, n = gpu_decode(t, 0.25, act)
+        ref, total = O.decode(t, 0.25, act)
+        assert int(n[0]) == total and same(V.candidates_to_numpy(c, n)[0], ref.view(V.CAND_DTYPE))
+
+
+def test_decode_all_pass_and_cap():
+    t = synth.logits_tensor(4)
+    c, n = gpu_decode(t, -1.0, cap=4096)            # every row passes: count 25200 > cap
+    ref, total = O.decode(t, -1.0, cap=4096)
+    assert int(n[0]) == total == 25200
+    assert same(V.candidates_to_numpy(c, n)[0], ref.view(V.CAND_DTYPE))
+    c, n = gpu_decode(t, 2.0)                       # nothing passes
+    assert int(n[0]) == 0
+
+
+def test_decode_batch_matches_singles():
+    ts = np.stack([synth.logits_tensor(s, adversarial=(s == 0)) for s in range(6)])
+    c, n = gpu_decode(ts, 0.5)
+    lists = V.candidates_to_numpy(c, n)
+    for i in range(6):
+        ref, total = O.decode(ts[i], 0.5)
+        assert int(n[i]) == total and same(lists[i], ref.view(V.CAND_DTYPE))
+
+
+def full_post(ts, thr, iou, max_det, act=V.ACT_RAW, cap=4096, agnostic=False):
+    c, n = gpu_decode(ts, thr, act, cap)
+    d, m = V.nms_classwise(c, n, iou, max_det, class_agnostic=agnostic)
+    torch.cuda.synchronize()
+    return V.candidates_to_numpy(d, m)
+
+
+@pytest.mark.parametrize("act", [V.ACT_RAW, V.ACT_SIGMOID, V.ACT_SOFTMAX])
+def test_decode_nms_bitexact_batch(act):
+    ts = np.stack([synth.logits_tensor(s, adversarial=(s % 2 == 0), as_logit=(act != V.ACT_RAW)) for s in range(8)])
+    got = full_post(ts, 0.5, 0.5, 500, act)
+    for i in range(8):
+        c, _ = O.decode(ts[i], 0.5, act, cap=4096)
+        ref = O.nms_classwise(c, 0.5, 500)
+        assert same(got[i], ref.view(V.CAND_DTYPE)), i
+
+
+@pytest.mark.parametrize("iou,max_det", [(0.0, 500), (0.3, 7), (0.7, 500), (1.0, 500)])
+def test_nms_thresholds_and_caps(iou, max_det):
+    t = synth.logits_tensor(5, adversarial=True, objects=80, dups=20)
+    got = full_post(t, 0.5, iou, max_det)[0]
+    c, _ = O.decode(t, 0.5)
+    assert same(got, O.nms_classwise(c, iou, max_det).view(V.CAND_DTYPE))
+
+
+def test_nms_large_dense_crowd():
+    # 4000 candidates, few classes, heavy overlap: exercises many 64-blocks and the sweep
+    t = synth.logits_tensor(6, objects=100, dups=40, num_classes=4)
+    got = full_post(t, 0.5, 0.45, 1000)[0]
+    c, total = O.decode(t, 0.5, cap=4096)
+    assert total == 4000
+    assert same(got, O.nms_classwise(c, 0.45, 1000).view(V.CAND_DTYPE))
+
+
+def test_nms_idempotent_on_gpu():
+    t = synth.logits_tensor(7)
+    c, n = gpu_decode(t, 0.5)
+    d, m = V.nms_classwise(c, n, 0.5, 500)
+    d2, m2 = V.nms_classwise(d, m, 0.5, 500)
+    torch.cuda.synchronize()
+    assert same(V.candidates_to_numpy(d, m)[0], V.candidates_to_numpy(d2, m2)[0])
+
+
+def test_nms_empty_frames():
+    ts = np.stack([synth.logits_tensor(8), synth.logits_tensor(9)])
+    ts[1, :, 4] = 0.0
+    got = full_post(ts, 0.5, 0.5, 100)
+    assert len(got[1]) == 0 and len(got[0]) > 0
+
+
+def test_cuda_tensor_nms_reference_signature():
+    # tk_cuda_tensor_nms (src/gpu/extensions/cuda/tk_cuda_tensor_ops.h:513-522): class-agnostic, score >= thr
+    rng = np.random.default_rng(0)
+    k = 1500
+    boxes = np.concatenate([rng.uniform(0, 500, (k, 2)), rng.uniform(5, 120, (k, 2))], axis=1).astype(np.float32)
+    scores = rng.uniform(0, 1, k).astype(np.float32)
+    scores[10] = 0.25                                   # == threshold: kept by >=
+    cands = np.zeros(k, O.CAND_DTYPE)
+    cands["index"] = np.arange(k)
+    cands["x"], cands["y"], cands["w"], cands["h"] = boxes.astype(np.int32).T
+    cands["confidence"] = scores
+    ref = O.nms_classwise(cands[scores >= 0.25], 0.4, 200)
+    with V.CudaDispatcher(0) as disp:
+        bb, bs, bi = disp.malloc(boxes.nbytes), disp.malloc(scores.nbytes), disp.malloc(200 * 4)
+        disp.upload_async(bb, boxes)
+        disp.upload_async(bs, scores)
+        n = disp.tensor_nms(bb, bs, k, bi, 200, 0.4, 0.25)
+        idx = np.full(200, -7, np.int32)
+        disp.download_async(idx, bi)
+        disp.synchronize()
+        for b in (bb, bs, bi):
+            disp.free(b)
+    assert n == len(ref)
+    assert np.array_equal(idx[:n], ref["index"]) and np.all(idx[n:] == -1)

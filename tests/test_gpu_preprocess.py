@@ -1,0 +1,145 @@
+"""GPU parity: fused pre-process kernel (through the C-ABI) vs the oracle / golden vectors."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import oracle as O
+from trackiellm_b200 import vision as V
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden.npz"))
+ATOL, RTOL = 1e-5, 1e-5          # fp32 bar of the north star: |a-b| <= atol + rtol*|ref|
+F16_TOL = 1e-2                   # fp16 bar of the north star
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def run(frames, ow, oh, **kw):
+    d = torch.from_numpy(np.ascontiguousarray(frames)).cuda()
+    out = V.preprocess_batch(d, ow, oh, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("name,ow,oh", [("pre_small_a", 40, 40), ("pre_small_b", 20, 12), ("pre_small_ramp", 32, 32)])
+def test_golden_small_bitexact(name, ow, oh):
+    got = run(G[name + "_in"][None], ow, oh)[0]
+    assert np.array_equal(bits(got), bits(G[name + "_out"]))
+
+
+@pytest.mark.parametrize("name,w,h,seed,kind", [
+    ("pre_cfg1_zeros", 640, 480, 0, "zeros"), ("pre_cfg1_random", 640, 480, 0, "random"),
+    ("pre_cfg1_ramp", 640, 480, 0, "ramp"), ("pre_cfg1_white", 640, 480, 0, "white"),
+    ("pre_1080p_random", 1920, 1080, 7, "random")])
+def test_golden_sha_reference_entry_points(name, w, h, seed, kind):
+    fr = synth.rgb_frame(w, h, seed, kind)
+    want = G[name + "_sha256"].tobytes()
+    # (1) the reference's host API, (2) the reference's GPU launcher, (3) the batched kernel
+    a = V.preprocessor_resize_and_normalize_to_chw(fr, 640, 640)
+    b = V.kernels_preprocess_image(torch.from_numpy(fr).cuda(), 640, 640).cpu().numpy()
+    c = run(fr[None], 640, 640)[0]
+    for got in (a, b, c):
+        assert hashlib.sha256(np.ascontiguousarray(got).tobytes()).digest() == want
+
+
+@pytest.mark.parametrize("w,h,ow,oh", [(640, 480, 640, 640), (1920, 1080, 640, 640), (333, 257, 640, 640), (64, 48, 640, 640),
+                                       (1920, 1080, 256, 256), (1920, 1080, 641, 333), (2, 2, 9, 5), (3840, 2160, 640, 640),
+                                       (640, 640, 640, 640), (100, 1000, 37, 1)])
+@pytest.mark.parametrize("arith", [V.ARITH_EXACT, V.ARITH_FAST])
+def test_fp32_vs_oracle(w, h, ow, oh, arith):
+    fr = np.stack([synth.rgb_frame(w, h, s) for s in (0, 1)])
+    got = run(fr, ow, oh, arith=arith)
+    for i in range(2):
+        ref = O.preprocess_rgb8(fr[i], ow, oh)
+        if arith == V.ARITH_EXACT:
+            assert np.array_equal(bits(got[i]), bits(ref))
+        else:
+            assert np.all(np.abs(got[i] - ref) <= ATOL + RTOL * np.abs(ref))
+
+
+@pytest.mark.parametrize("arith", [V.ARITH_EXACT, V.ARITH_FAST])
+def test_fp16_vs_oracle(arith):
+    fr = np.stack([synth.rgb_frame(1920, 1080, s) for s in range(3)])
+    got = run(fr, 640, 640, out_dtype=torch.float16, arith=arith)
+    for i in range(3):
+        ref32 = O.preprocess_rgb8(fr[i], 640, 640)
+        ref16 = O.f32_to_f16(ref32)
+        if arith == V.ARITH_EXACT:
+            assert np.array_equal(got[i].view(np.uint16), ref16.view(np.uint16))
+        g = got[i].astype(np.float32)
+        assert np.all(np.abs(g - ref32) <= F16_TOL + F16_TOL * np.abs(ref32))
+
+
+def test_batch_equals_singles_and_is_deterministic():
+    fr = np.stack([synth.rgb_frame(1920, 1080, s) for s in range(5)])
+    a = run(fr, 640, 640)
+    b = run(fr, 640, 640)
+    assert np.array_equal(bits(a), bits(b))
+    for i in range(5):
+        assert np.array_equal(bits(a[i]), bits(run(fr[i:i + 1], 640, 640)[0]))
+
+
+def test_stride_and_unaligned_fallback():
+    w, h = 301, 77                       # row = 903 B: not 16-byte aligned -> cooperative copy path
+    fr = synth.rgb_frame(w, h, 4)
+    ref = O.preprocess_rgb8(fr, 128, 64)
+    assert np.array_equal(bits(run(fr[None], 128, 64)[0]), bits(ref))
+    stride = 1024                        # padded rows, TMA-eligible
+    buf = np.zeros((1, h * stride), np.uint8)
+    buf[0].reshape(h, stride)[:, : w * 3] = fr.reshape(h, w * 3)
+    got = run(buf, 128, 64, width=w, height=h, stride=stride)[0]
+    assert np.array_equal(bits(got), bits(ref))
+
+
+def test_rgba8():
+    fr = synth.rgb_frame(320, 200, 6)
+    rgba = np.concatenate([fr, np.full((200, 320, 1), 77, np.uint8)], axis=2)
+    got = run(rgba[None], 96, 96, fmt=V.PIXEL_RGBA8)[0]
+    assert np.array_equal(bits(got), bits(O.preprocess_rgb8(fr, 96, 96)))
+
+
+@pytest.mark.parametrize("w,h", [(3840, 2160), (640, 480), (130, 66)])
+def test_i420(w, h):
+    buf = synth.i420_frame(w, h, 8)
+    rgb = O.i420_to_rgb8(buf, w, h)
+    got = run(buf[None], 640, 640, width=w, height=h, fmt=V.PIXEL_I420)[0]
+    assert np.array_equal(bits(got), bits(O.preprocess_rgb8(rgb, 640, 640)))
+    got16 = run(buf[None], 640, 640, width=w, height=h, fmt=V.PIXEL_I420, out_dtype=torch.float16, arith=V.ARITH_EXACT)[0]
+    assert np.array_equal(got16.view(np.uint16), O.f32_to_f16(O.preprocess_rgb8(rgb, 640, 640)).view(np.uint16))
+
+
+@pytest.mark.parametrize("w,h", [(640, 480), (1920, 1080), (480, 640)])
+def test_letterbox(w, h):
+    fr = synth.rgb_frame(w, h, 2)
+    got = run(fr[None], 640, 640, resize=V.RESIZE_LETTERBOX, pad_value=114.0)[0]
+    ref = O.preprocess_rgb8(fr, 640, 640, resize=O.RESIZE_LETTERBOX, pad_value=114.0)
+    assert np.array_equal(bits(got), bits(ref))
+
+
+def test_error_codes():
+    from trackiellm_b200 import _capi as capi
+    d = torch.zeros((1, 1, 8, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(capi.TkError) as e:
+        V.preprocess_batch(d, 8, 8)
+    assert e.value.code == capi.TK_ERROR_INVALID_DIMENSIONS
+    with pytest.raises(capi.TkError):
+        V.preprocess_batch(torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device="cuda"), 8, 8, std=(0.0, 1.0, 1.0))
+
+
+def test_full_size_property_constant_frames():
+    # size-independent property at BASELINE cfg-2 size: a constant frame maps to a constant tensor
+    fr = np.full((4, 1080, 1920, 3), 0, np.uint8)
+    for i, v in enumerate((0, 1, 128, 255)):
+        fr[i] = v
+    got = run(fr, 640, 640)
+    for i, v in enumerate((0, 1, 128, 255)):
+        for c in range(3):
+            want = ((np.float32(v) * np.float32(1.0 / 255.0)) - np.float32(O.IMAGENET_MEAN[c])) / np.float32(O.IMAGENET_STD[c])
+            plane = got[i, c]
+            assert np.all(np.abs(plane - want) <= ATOL + RTOL * abs(want))

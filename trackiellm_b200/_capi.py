@@ -96,6 +96,12 @@ class ColorParams(C.Structure):            # tk_b200_color_params_t
                 ("d_color_ids", C.c_void_p), ("d_bins", C.c_void_p)]
 
 
+class DoorParams(C.Structure):             # tk_b200_door_params_t
+    _fields_ = [("d_frame", C.c_void_p), ("width", C.c_uint32), ("height", C.c_uint32),
+                ("stride_bytes", C.c_uint32), ("d_boxes", C.c_void_p), ("num_boxes", C.c_uint32),
+                ("d_states", C.c_void_p), ("d_edge_pixels", C.c_void_p)]
+
+
 class TensorDescriptor(C.Structure):       # tk_tensor_descriptor_t
     _fields_ = [("buffer", C.c_void_p), ("type", C.c_int), ("layout", C.c_int), ("dimensions", C.c_uint32),
                 ("shape", C.c_uint32 * 8), ("stride", C.c_size_t * 8), ("data_size_bytes", C.c_size_t),
@@ -133,10 +139,17 @@ def lib() -> C.CDLL:
         _lib.tk_error_to_string.restype = C.c_char_p
         _lib.tk_error_to_string.argtypes = [C.c_int]
         _lib.tk_b200_version.restype = C.c_char_p
-        for name in ("tk_b200_color_name",):
-            if hasattr(_lib, name):
-                getattr(_lib, name).restype = C.c_char_p
-                getattr(_lib, name).argtypes = [C.c_uint32]
+        _lib.tk_b200_color_name.restype = C.c_char_p
+        _lib.tk_b200_color_name.argtypes = [C.c_uint32]
+        _lib.tk_b200_buffer_device_ptr.restype = C.c_void_p
+        _lib.tk_b200_buffer_device_ptr.argtypes = [C.c_void_p]
+        _lib.tk_b200_buffer_size.restype = C.c_size_t
+        _lib.tk_b200_buffer_size.argtypes = [C.c_void_p]
+        _lib.tk_b200_dispatch_stream.restype = C.c_void_p
+        _lib.tk_b200_dispatch_stream.argtypes = [C.c_void_p]
+        _lib.tk_b200_dispatch_device.argtypes = [C.c_void_p]
+        _lib.tk_b200_host_free.argtypes = [C.c_void_p]
+        _lib.tk_b200_host_free.restype = None
     return _lib
 
 

@@ -1,0 +1,201 @@
+// nms.cu — class-wise greedy IoU non-maximum suppression, one CTA per frame.
+//
+// Completes  the NMS step the reference leaves as a comment
+//              (src/vision/tk_object_detector.c:357) with calculate_iou a stub
+//              (:371), and replaces tk_cuda_nms_kernel / tk_cuda_tensor_nms
+//              (src/gpu/extensions/cuda/tk_cuda_tensor_ops.cu:452-482, :858-889),
+//              which only filter by score.
+// Semantics:
+//   IoU on truncated integer rects exactly as src/vision/src/object_analysis.rs:71-91;
+//   order (confidence desc by IEEE total order, proposal index asc);
+//   box k is dropped iff an already KEPT box j<k of the same class has IoU > thr
+//   (strict; predicate of src/gpu/metal/tk_metal_kernels.metal:868-875 made sequential);
+//   output = kept boxes in sorted order, truncated to max_detections.
+//
+// B200 design (latency-bound, filled by frame-level parallelism):
+//   * candidates -> 64-bit keys (~order_key(conf) << 32 | index) + position payload,
+//     bitonic sort in shared memory;
+//   * sorted boxes/classes staged in shared memory;
+//   * the suppression matrix is evaluated in 64-column blocks: each thread builds
+//     one 64-bit row of the diagonal block (bitmask matrix), one thread resolves
+//     the block with a register-carried kept-mask, then all threads sweep the
+//     remaining candidates against the block's kept boxes;
+//   * kept flags -> ballot/prefix compaction in sorted order.
+#include "tk_common.cuh"
+
+namespace tkb {
+
+static constexpr int kNmsThreads = 512;
+static constexpr int kNmsWarps = kNmsThreads / 32;
+static constexpr uint32_t kNmsMaxK = 4096;
+
+struct NmsK {
+    const tk_b200_candidate_t* cands;
+    const uint32_t* counts;
+    tk_b200_candidate_t* dets;
+    uint32_t* num_dets;
+    uint32_t cap, max_det, Kp;      // Kp: power of two >= cap (>= 64)
+    float thr;
+    int agnostic;
+};
+
+// src/vision/src/object_analysis.rs:71-91 (i32 arithmetic wraps like release-mode Rust).
+__device__ __forceinline__ float iou_rect(int4 a, int4 b) {
+    int x_left = max(a.x, b.x), y_top = max(a.y, b.y);
+    int x_right = min((int)((unsigned)a.x + (unsigned)a.z), (int)((unsigned)b.x + (unsigned)b.z));
+    int y_bottom = min((int)((unsigned)a.y + (unsigned)a.w), (int)((unsigned)b.y + (unsigned)b.w));
+    if (x_right < x_left || y_bottom < y_top) return 0.0f;
+    float inter = __fmul_rn((float)(int)((unsigned)x_right - (unsigned)x_left),
+                            (float)(int)((unsigned)y_bottom - (unsigned)y_top));
+    float a1 = (float)(int)((unsigned)a.z * (unsigned)a.w);
+    float a2 = (float)(int)((unsigned)b.z * (unsigned)b.w);
+    float uni = __fsub_rn(__fadd_rn(a1, a2), inter);
+    return uni > 0.0f ? __fdiv_rn(inter, uni) : 0.0f;
+}
+
+__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(dsm);          // [Kp]
+    int4* box = reinterpret_cast<int4*>(keys + k.Kp);                               // [Kp]
+    uint32_t* pos = reinterpret_cast<uint32_t*>(box + k.Kp);                        // [Kp] position in the input list
+    uint32_t* cls = pos + k.Kp;                                                     // [Kp]
+    uint8_t* dead = reinterpret_cast<uint8_t*>(cls + k.Kp);                         // [Kp]
+    __shared__ unsigned long long diag[64];
+    __shared__ unsigned long long blk_kept;
+    __shared__ uint32_t warp_tot[kNmsWarps];
+
+    const uint32_t frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const tk_b200_candidate_t* in = k.cands + (size_t)frame * k.cap;
+    tk_b200_candidate_t* out = k.dets + (size_t)frame * k.max_det;
+    const uint32_t K = min(k.counts[frame], k.cap);
+    if (K == 0 || k.max_det == 0) { if (tid == 0) k.num_dets[frame] = 0; return; }
+    uint32_t Kp = 64;
+    while (Kp < K) Kp <<= 1;                                       // sort only what this frame needs
+
+    // ---- keys ---------------------------------------------------------------
+    for (uint32_t i = tid; i < Kp; i += kNmsThreads) {
+        unsigned long long key = ~0ull;
+        if (i < K) {
+            uint32_t ck = tk_dm_float_order_key(in[i].confidence);
+            key = ((unsigned long long)(~ck) << 32) | (uint32_t)in[i].index;
+        }
+        keys[i] = key; pos[i] = i;
+    }
+    __syncthreads();
+    // ---- bitonic sort (ascending key == confidence desc, index asc) ----------
+    for (uint32_t kk = 2; kk <= Kp; kk <<= 1) {
+        for (uint32_t j = kk >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = tid; t < (Kp >> 1); t += kNmsThreads) {
+                uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                uint32_t l = i | j;
+                unsigned long long a = keys[i], b = keys[l];
+                bool up = (i & kk) == 0;
+                if ((a > b) == up) {
+                    keys[i] = b; keys[l] = a;
+                    uint32_t pa = pos[i]; pos[i] = pos[l]; pos[l] = pa;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // Equal keys (same confidence and same index) can only be distinct input
+    // positions holding identical proposals; any order among them gives the same output.
+    // ---- stage sorted boxes -------------------------------------------------
+    for (uint32_t i = tid; i < K; i += kNmsThreads) {
+        const tk_b200_candidate_t& c = in[pos[i]];
+        box[i] = make_int4(c.bbox.x, c.bbox.y, c.bbox.w, c.bbox.h);
+        cls[i] = k.agnostic ? 0u : c.class_id;
+        dead[i] = 0;
+    }
+    __syncthreads();
+
+    // ---- blocked greedy suppression -----------------------------------------
+    for (uint32_t b0 = 0; b0 < K; b0 += 64) {
+        const uint32_t bn = min(64u, K - b0);
+        // (a) diagonal block of the bitmask matrix: bit j of diag[i] <=> j < i suppresses i
+        if (tid < 64) {
+            unsigned long long m = 0;
+            if (tid < bn && !dead[b0 + tid]) {
+                const int4 me = box[b0 + tid]; const uint32_t mc = cls[b0 + tid];
+                for (uint32_t j = 0; j < tid; ++j)
+                    if (cls[b0 + j] == mc && !dead[b0 + j] && iou_rect(box[b0 + j], me) > k.thr) m |= 1ull << j;
+            }
+            diag[tid] = m;
+        }
+        __syncthreads();
+        // (b) sequential resolve of the 64 candidates with the kept-mask in a register
+        if (tid == 0) {
+            unsigned long long kept = 0;
+#pragma unroll 8
+            for (uint32_t i = 0; i < 64; ++i) {
+                bool alive = i < bn && !dead[b0 + i];
+                if (alive && (diag[i] & kept) == 0) kept |= 1ull << i;
+                else if (i < bn) dead[b0 + i] = 1;
+            }
+            blk_kept = kept;
+        }
+        __syncthreads();
+        // (c) sweep: kept boxes of this block suppress every later candidate
+        const unsigned long long kept = blk_kept;
+        if (kept) {
+            for (uint32_t i = b0 + 64 + tid; i < K; i += kNmsThreads) {
+                if (dead[i]) continue;
+                const int4 me = box[i]; const uint32_t mc = cls[i];
+                unsigned long long rem = kept;
+                while (rem) {
+                    const uint32_t j = __ffsll((long long)rem) - 1;
+                    rem &= rem - 1;
+                    if (cls[b0 + j] == mc && iou_rect(box[b0 + j], me) > k.thr) { dead[i] = 1; break; }
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- ordered compaction of the survivors --------------------------------
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < K; base += kNmsThreads) {
+        const uint32_t i = base + tid;
+        const bool keep = i < K && !dead[i];
+        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_tot[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t before = 0, tot = 0;
+#pragma unroll
+        for (int w = 0; w < kNmsWarps; ++w) { uint32_t t = warp_tot[w]; before += (uint32_t)w < warp ? t : 0u; tot += t; }
+        const uint32_t o = run + before + __popc(bal & ((1u << lane) - 1u));
+        if (keep && o < k.max_det) out[o] = in[pos[i]];
+        run += tot;
+        __syncthreads();
+        if (run >= k.max_det) break;
+    }
+    if (tid == 0) k.num_dets[frame] = min(run, k.max_det);
+}
+
+}  // namespace tkb
+
+using namespace tkb;
+
+extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* p, cudaStream_t stream) {
+    if (!p || !p->d_counts || !p->d_num_detections || (!p->d_candidates && p->max_candidates) ||
+        (!p->d_detections && p->max_detections))
+        return TK_ERROR_INVALID_ARGUMENT;
+    if (p->num_frames == 0) return TK_SUCCESS;
+    if (p->max_candidates > kNmsMaxK) {
+        tk_error_set_detail("nms: max_candidates %u exceeds the %u candidates one CTA sorts in shared memory",
+                            p->max_candidates, kNmsMaxK);
+        return TK_ERROR_NOT_IMPLEMENTED;
+    }
+    const DeviceInfo* dev = device_info();
+    if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
+    NmsK k{};
+    k.cands = p->d_candidates; k.counts = p->d_counts; k.dets = p->d_detections; k.num_dets = p->d_num_detections;
+    k.cap = p->max_candidates; k.max_det = p->max_detections;
+    k.Kp = 64; while (k.Kp < k.cap) k.Kp <<= 1;
+    k.thr = p->iou_threshold; k.agnostic = p->class_agnostic;
+    const size_t smem = (size_t)k.Kp * (8 + 16 + 4 + 4 + 1);
+    if (smem > 48 * 1024)
+        TK_CUDA_TRY(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    nms_kernel<<<p->num_frames, kNmsThreads, smem, stream>>>(k);
+    return launch_status("nms_kernel");
+}

@@ -1,0 +1,174 @@
+// rows.cu — row softmax with fused first-max argmax.
+//
+// Replaces  tk_cuda_softmax_kernel / tk_kernels_softmax
+//             (src/gpu/cuda/tk_cuda_kernels.cu:312-393): one block per row with
+//             blockDim == num_cols and a halving tree that is only correct for
+//             power-of-two num_cols (:331-336) and rejects num_cols > 1024 (:369).
+// Parity target: softmax_cpu of tests/tk_gpu_softmax_test.cpp:24-51 — max :33-38,
+//             sum of exp(x-max) in INDEX ORDER :41-44, divide :47-49.
+//
+// B200 design (HBM-bound: 8 B per element):
+//   * cols <= 128 (the detector's 80 classes): a warp owns a tile of 32 rows.
+//     The tile is loaded flat and fully coalesced into shared memory with an odd
+//     row stride (conflict-free), then LANE r walks ROW r: the running max, the
+//     first-max index and the index-ordered sum are sequential per row exactly as
+//     in the reference loop, yet 32 rows advance in lock-step.  The normalised
+//     tile is written back flat and coalesced.
+//   * larger rows: a warp per row; exponentials land in a per-warp shared buffer
+//     and are summed in index order (cols <= 4096), or by a shuffle tree beyond.
+//   * exp is tk_dm_expf (bit-identical to the oracle's deterministic mode and
+//     within 2 ulp of libm, inside the reference test's 1e-6 absolute bound).
+#include "tk_common.cuh"
+
+namespace tkb {
+
+static constexpr int kRowThreads = 256;
+static constexpr int kRowWarps = kRowThreads / 32;
+static constexpr uint32_t kTileMaxCols = 128;
+static constexpr uint32_t kSeqMaxCols = 4096;
+
+struct RowK {
+    const float* in;
+    float* out;          // may be null
+    uint32_t* amax;      // may be null
+    uint32_t rows, cols, stride;   // stride: odd smem row stride (tile kernel)
+    uint32_t ntiles;
+};
+
+__global__ void __launch_bounds__(kRowThreads) softmax_tile_kernel(const RowK k) {
+    extern __shared__ __align__(16) float tsm[];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* tile = tsm + (size_t)warp * 32 * k.stride;
+    for (uint32_t t = blockIdx.x * kRowWarps + warp; t < k.ntiles; t += gridDim.x * kRowWarps) {
+        const uint32_t r0 = t * 32;
+        const uint32_t nr = min(32u, k.rows - r0);
+        const uint32_t nel = nr * k.cols;
+        const float* src = k.in + (size_t)r0 * k.cols;
+        // flat coalesced load; (row, col) advanced incrementally (32 = a*cols + b)
+        const uint32_t step_r = 32 / k.cols, step_c = 32 % k.cols;
+        uint32_t rr = lane / k.cols, cc = lane % k.cols;
+        for (uint32_t e = lane; e < nel; e += 32) {
+            tile[rr * k.stride + cc] = __ldcs(src + e);
+            rr += step_r; cc += step_c;
+            if (cc >= k.cols) { cc -= k.cols; ++rr; }
+        }
+        __syncwarp();
+        float sum = 1.0f;
+        if (lane < nr) {
+            float* row = tile + lane * k.stride;
+            float mx = row[0];
+            uint32_t best = 0;
+            for (uint32_t j = 1; j < k.cols; ++j) {
+                float v = row[j];
+                if (v > mx) { mx = v; best = j; }
+            }
+            if (k.amax) k.amax[r0 + lane] = best;
+            if (k.out) {
+                sum = 0.0f;
+                for (uint32_t j = 0; j < k.cols; ++j) {
+                    float e = tk_dm_expf(__fsub_rn(row[j], mx));
+                    row[j] = e;
+                    sum = __fadd_rn(sum, e);
+                }
+            }
+        }
+        __syncwarp();
+        if (k.out) {
+            float* dst = k.out + (size_t)r0 * k.cols;
+            rr = lane / k.cols; cc = lane % k.cols;
+            for (uint32_t e0 = 0; e0 < nel; e0 += 32) {      // uniform trip count: the shuffle needs all lanes
+                const uint32_t e = e0 + lane;
+                float s = __shfl_sync(0xffffffffu, sum, rr & 31);
+                if (e < nel) __stcs(dst + e, __fdiv_rn(tile[rr * k.stride + cc], s));
+                rr += step_r; cc += step_c;
+                if (cc >= k.cols) { cc -= k.cols; ++rr; }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kRowThreads) softmax_row_kernel(const RowK k) {
+    extern __shared__ __align__(16) float rsm[];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool seq = k.cols <= kSeqMaxCols;
+    float* ebuf = rsm + (size_t)warp * (seq ? k.cols : 0);
+    for (uint32_t r = blockIdx.x * kRowWarps + warp; r < k.rows; r += gridDim.x * kRowWarps) {
+        const float* row = k.in + (size_t)r * k.cols;
+        // sequential-scan semantics: mx = x[0]; if (x[j] > mx) ...  (NaN at 0 sticks, NaN elsewhere ignored)
+        float mv = 0.0f; uint32_t mi = 0xffffffffu;
+        for (uint32_t j = lane; j < k.cols; j += 32) {
+            float v = __ldg(row + j);
+            if (j == 0 || (v == v && !(mv != mv) && (mi == 0xffffffffu || v > mv))) { mv = v; mi = j; }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, mv, d);
+            uint32_t oi = __shfl_xor_sync(0xffffffffu, mi, d);
+            if (oi == 0xffffffffu || (mi != 0xffffffffu && mv != mv)) continue;
+            if (mi == 0xffffffffu || ov != ov || ov > mv || (ov == mv && oi < mi)) { mv = ov; mi = oi; }
+        }
+        if (lane == 0 && k.amax) k.amax[r] = mi;
+        if (!k.out) continue;
+        float sum = 0.0f;
+        if (seq) {
+            for (uint32_t j = lane; j < k.cols; j += 32) ebuf[j] = tk_dm_expf(__fsub_rn(__ldg(row + j), mv));
+            __syncwarp();
+            if (lane == 0) for (uint32_t j = 0; j < k.cols; ++j) sum = __fadd_rn(sum, ebuf[j]);
+            sum = __shfl_sync(0xffffffffu, sum, 0);
+            for (uint32_t j = lane; j < k.cols; j += 32) __stcs(k.out + (size_t)r * k.cols + j, __fdiv_rn(ebuf[j], sum));
+            __syncwarp();
+        } else {
+            for (uint32_t j = lane; j < k.cols; j += 32) sum = __fadd_rn(sum, tk_dm_expf(__fsub_rn(__ldg(row + j), mv)));
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) sum = __fadd_rn(sum, __shfl_xor_sync(0xffffffffu, sum, d));
+            for (uint32_t j = lane; j < k.cols; j += 32)
+                __stcs(k.out + (size_t)r * k.cols + j, __fdiv_rn(tk_dm_expf(__fsub_rn(__ldg(row + j), mv)), sum));
+        }
+    }
+}
+
+static tk_error_code_t launch_rows(const float* in, float* out, uint32_t* amax, uint32_t rows, uint32_t cols, cudaStream_t stream) {
+    const DeviceInfo* dev = device_info();
+    if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
+    RowK k{};
+    k.in = in; k.out = out; k.amax = amax; k.rows = rows; k.cols = cols;
+    if (cols <= kTileMaxCols) {
+        k.stride = cols | 1u;
+        k.ntiles = (rows + 31) / 32;
+        const size_t smem = (size_t)kRowWarps * 32 * k.stride * 4;
+        TK_CUDA_TRY(cudaFuncSetAttribute(softmax_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+        const uint32_t per_sm = smem ? (uint32_t)((size_t)200 * 1024 / smem) : 8u;
+        uint32_t grid = (k.ntiles + kRowWarps - 1) / kRowWarps;
+        const uint32_t cap = (uint32_t)dev->sm_count * (per_sm ? per_sm : 1u);
+        if (grid > cap) grid = cap;
+        softmax_tile_kernel<<<grid, kRowThreads, smem, stream>>>(k);
+        return launch_status("softmax_tile_kernel");
+    }
+    const size_t smem = cols <= kSeqMaxCols ? (size_t)kRowWarps * cols * 4 : 0;
+    if (smem > 48 * 1024)
+        TK_CUDA_TRY(cudaFuncSetAttribute(softmax_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    uint32_t grid = (rows + kRowWarps - 1) / kRowWarps;
+    const uint32_t cap = (uint32_t)dev->sm_count * 8u;
+    if (grid > cap) grid = cap;
+    softmax_row_kernel<<<grid, kRowThreads, smem, stream>>>(k);
+    return launch_status("softmax_row_kernel");
+}
+
+}  // namespace tkb
+
+using namespace tkb;
+
+// src/gpu/cuda/tk_cuda_kernels.cu:362-393 (argument checks and codes kept; any num_cols accepted).
+extern "C" tk_error_code_t tk_kernels_softmax(const tk_softmax_params_t* p, cudaStream_t stream) {
+    if (!p || !p->d_input_tensor || !p->d_output_tensor) return TK_ERROR_INVALID_ARGUMENT;
+    if (p->num_rows == 0 || p->num_cols == 0) return TK_ERROR_INVALID_DIMENSIONS;
+    return launch_rows(static_cast<const float*>(p->d_input_tensor), static_cast<float*>(p->d_output_tensor), nullptr,
+                       p->num_rows, p->num_cols, stream);
+}
+
+extern "C" tk_error_code_t tk_kernels_argmax_rows(const tk_b200_argmax_params_t* p, cudaStream_t stream) {
+    if (!p || !p->d_input || (!p->d_softmax && !p->d_argmax)) return TK_ERROR_INVALID_ARGUMENT;
+    if (p->num_rows == 0 || p->num_cols == 0) return TK_ERROR_INVALID_DIMENSIONS;
+    return launch_rows(p->d_input, p->d_softmax, p->d_argmax, p->num_rows, p->num_cols, stream);
+}

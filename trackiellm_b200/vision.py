@@ -186,3 +186,124 @@ def dominant_color(frame: torch.Tensor, boxes: torch.Tensor, want_bins: bool = F
     with torch.cuda.device(frame.device):
         capi.check(capi.lib().tk_kernels_dominant_color(C.byref(p), _stream()), "tk_kernels_dominant_color")
     return ids, bins
+
+
+def door_state(frame: torch.Tensor, boxes: torch.Tensor, want_edges: bool = False):
+    """tk_kernels_door_state.  Returns (states int32 [M] (1 = closed), edge counts int32 [M] or None)."""
+    _require_cuda(frame, "frame")
+    _require_cuda(boxes, "boxes")
+    h, w = frame.shape[0], frame.shape[1]
+    m = boxes.shape[0]
+    st = torch.empty((m,), dtype=torch.int32, device=frame.device)
+    ed = torch.empty((m,), dtype=torch.int32, device=frame.device) if want_edges else None
+    p = capi.DoorParams(frame.data_ptr(), w, h, w * 3, boxes.data_ptr(), m, st.data_ptr(),
+                        ed.data_ptr() if ed is not None else None)
+    with torch.cuda.device(frame.device):
+        capi.check(capi.lib().tk_kernels_door_state(C.byref(p), _stream()), "tk_kernels_door_state")
+    return st, ed
+
+
+def _host_frame(frame: np.ndarray) -> tuple[capi.VideoFrame, np.ndarray]:
+    frame = np.ascontiguousarray(frame, dtype=np.uint8)
+    h, w = frame.shape[:2]
+    return capi.VideoFrame(w, h, w * 3, PIXEL_RGB8, frame.ctypes.data), frame
+
+
+def _classify_host(fn_name: str, frame: np.ndarray, bbox) -> str:
+    vf, keep = _host_frame(frame)
+    r = capi.Rect(*[int(v) for v in bbox])
+    s = C.c_void_p()
+    capi.check(getattr(capi.lib(), fn_name)(C.byref(vf), C.byref(r), C.byref(s)), fn_name)
+    name = C.string_at(s.value).decode()
+    C.CDLL(None).free(s)
+    return name
+
+
+def classify_dominant_color(frame: np.ndarray, bbox) -> str:
+    """tk_classify_dominant_color (src/vision/tk_attribute_classifier.h): HOST frame, returns the colour name."""
+    return _classify_host("tk_classify_dominant_color", frame, bbox)
+
+
+def classify_door_state(frame: np.ndarray, bbox) -> str:
+    """tk_classify_door_state: HOST frame, returns "open" or "closed"."""
+    return _classify_host("tk_classify_door_state", frame, bbox)
+
+
+def kernels_postprocess_depth_map(raw: torch.Tensor, scale: float, shift: float) -> torch.Tensor:
+    """tk_kernels_postprocess_depth_map (src/gpu/cuda/tk_cuda_kernels.h:64)."""
+    _require_cuda(raw, "raw")
+    out = torch.empty_like(raw)
+    p = capi.DepthPostParams(raw.data_ptr(), raw.shape[1], raw.shape[0], out.data_ptr(), scale, shift)
+    with torch.cuda.device(raw.device):
+        capi.check(capi.lib().tk_kernels_postprocess_depth_map(C.byref(p), _stream()), "tk_kernels_postprocess_depth_map")
+    return out
+
+
+def kernels_depth_to_point_cloud(depth: torch.Tensor, fx: float, fy: float, cx: float, cy: float) -> torch.Tensor:
+    """tk_kernels_depth_to_point_cloud (src/gpu/cuda/tk_cuda_kernels.h:78) -> [H,W,3] f32."""
+    _require_cuda(depth, "depth")
+    h, w = depth.shape
+    out = torch.empty((h, w, 3), dtype=torch.float32, device=depth.device)
+    p = capi.DepthPointsParams(depth.data_ptr(), w, h, out.data_ptr(), fx, fy, cx, cy)
+    with torch.cuda.device(depth.device):
+        capi.check(capi.lib().tk_kernels_depth_to_point_cloud(C.byref(p), _stream()), "tk_kernels_depth_to_point_cloud")
+    return out
+
+
+class CudaDispatcher:
+    """tk_cuda_dispatch_* (src/gpu/cuda/tk_cuda_dispatch.h:72-171) as a context object."""
+
+    def __init__(self, device_id: int = 0):
+        self._h = C.c_void_p()
+        cfg = capi.DispatcherConfig(device_id)
+        capi.check(capi.lib().tk_cuda_dispatch_create(C.byref(self._h), C.byref(cfg)), "tk_cuda_dispatch_create")
+
+    def close(self) -> None:
+        if self._h:
+            capi.lib().tk_cuda_dispatch_destroy(C.byref(self._h))
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def malloc(self, size: int) -> C.c_void_p:
+        b = C.c_void_p()
+        capi.check(capi.lib().tk_cuda_dispatch_malloc(self._h, C.byref(b), C.c_size_t(size)), "tk_cuda_dispatch_malloc")
+        return b
+
+    def free(self, buf: C.c_void_p) -> None:
+        capi.lib().tk_cuda_dispatch_free(self._h, C.byref(buf))
+
+    def upload_async(self, buf, host: np.ndarray) -> None:
+        capi.check(capi.lib().tk_cuda_dispatch_upload_async(self._h, buf, host.ctypes.data_as(C.c_void_p),
+                                                            C.c_size_t(host.nbytes)), "tk_cuda_dispatch_upload_async")
+
+    def download_async(self, host: np.ndarray, buf) -> None:
+        capi.check(capi.lib().tk_cuda_dispatch_download_async(self._h, host.ctypes.data_as(C.c_void_p), buf,
+                                                              C.c_size_t(host.nbytes)), "tk_cuda_dispatch_download_async")
+
+    def synchronize(self) -> None:
+        capi.check(capi.lib().tk_cuda_dispatch_synchronize(self._h), "tk_cuda_dispatch_synchronize")
+
+    def device_ptr(self, buf) -> int:
+        return int(capi.lib().tk_b200_buffer_device_ptr(buf) or 0)
+
+    def preprocess_image(self, d_in, w, h, d_out, out_w, out_h, mean=IMAGENET_MEAN, std=IMAGENET_STD, stride=0) -> None:
+        p = capi.PreprocessParams(self.device_ptr(d_in), w, h, stride or w * 3, self.device_ptr(d_out), out_w, out_h,
+                                  _f3(mean), _f3(std))
+        capi.check(capi.lib().tk_cuda_dispatch_preprocess_image(self._h, C.byref(p)), "tk_cuda_dispatch_preprocess_image")
+
+    def tensor_nms(self, d_boxes, d_scores, num_boxes: int, d_indices, max_detections: int, iou_thr: float,
+                   score_thr: float) -> int:
+        """tk_cuda_tensor_nms (src/gpu/extensions/cuda/tk_cuda_tensor_ops.h:513-522)."""
+        tb = capi.TensorDescriptor(buffer=d_boxes, type=0, layout=2, dimensions=3)
+        tb.shape[0], tb.shape[1], tb.shape[2] = 1, num_boxes, 4
+        ts = capi.TensorDescriptor(buffer=d_scores, type=0, layout=2, dimensions=2)
+        ts.shape[0], ts.shape[1] = 1, num_boxes
+        n = C.c_uint32(0)
+        capi.check(capi.lib().tk_cuda_tensor_nms(self._h, C.byref(tb), C.byref(ts), d_indices, C.byref(n),
+                                                 C.c_uint32(max_detections), C.c_float(iou_thr), C.c_float(score_thr)),
+                   "tk_cuda_tensor_nms")
+        return int(n.value)
