@@ -124,6 +124,13 @@ TK_DM_FN int32_t tk_dm_f2i_trunc(float x) {
 #endif
 }
 
+/* NaN results are canonicalised to the quiet NaN 0x7fc00000: x86 SSE propagates
+ * the operand's payload while the GPU's FMUL returns 0x7fffffff, so an
+ * arithmetic NaN would otherwise differ in its bits between host and device. */
+TK_DM_FN float tk_dm_canon_nan(float x) {
+    return (x != x) ? tk_dm_bits_to_float(0x7fc00000u) : x;
+}
+
 /* Order-preserving map float -> u32 (total order on IEEE bit patterns:
  * -NaN < -inf < ... < -0 < +0 < ... < +inf < +NaN). */
 TK_DM_FN uint32_t tk_dm_float_order_key(float f) {

@@ -148,6 +148,13 @@ typedef struct {
     int                        class_agnostic; /* 0 = only equal class_id suppresses         */
     tk_b200_candidate_t*       d_detections;   /* [N][max_detections], (score desc, index asc) */
     uint32_t*                  d_num_detections; /* [N]                                      */
+    /* Optional coordinate restore of the kept boxes, model-input px -> source-frame
+     * px (completes the empty convert_to_original_coordinates,
+     * src/vision/tk_object_detector.c:76-79,365,372-375): x,w scaled by
+     * src_width/in_width, y,h by src_height/in_height in fp32, truncated.  All four
+     * zero = boxes stay in model-input px. */
+    uint32_t                   restore_src_width, restore_src_height;
+    uint32_t                   restore_in_width, restore_in_height;
 } tk_b200_nms_params_t;
 
 TK_NODISCARD tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* params, cudaStream_t stream);
@@ -190,6 +197,94 @@ typedef struct {
 
 TK_NODISCARD tk_error_code_t tk_kernels_door_state(const tk_b200_door_params_t* params, cudaStream_t stream);
 
+/* ------------------------------------------------------------------------ */
+/* Batched pipeline: pre-process + decode + class-wise NMS for a batch of     */
+/* frames of one geometry (the step BASELINE.json's metric counts).  The      */
+/* reference runs this one frame per call inside tk_object_detector_detect    */
+/* (src/vision/tk_object_detector.c:182-203: preprocess_frame :223-259,       */
+/* postprocess_detections :303-368); thresholds as tk_object_detector_config_t */
+/* (src/vision/tk_object_detector.h:44-58).                                    */
+/* ------------------------------------------------------------------------ */
+typedef struct tk_b200_pipeline_s tk_b200_pipeline_t;
+
+typedef struct {
+    int                   device_id;
+    uint32_t              max_batch;          /* most frames one process call may carry         */
+    uint32_t              chunk_frames;       /* frames per in-flight chunk of process_host; 0 = 8 */
+    /* frame geometry (all frames of a pipeline share it) */
+    uint32_t              input_width, input_height;
+    uint32_t              input_stride_bytes; /* 0 = tightly packed                              */
+    tk_pixel_format_e     input_format;       /* RGB8, RGBA8, I420                               */
+    /* model input tensor */
+    uint32_t              tensor_width, tensor_height;   /* 640 x 640, tk_vision_pipeline.c:368-378 */
+    tk_b200_out_type_e    tensor_type;
+    tk_b200_resize_mode_e resize_mode;
+    tk_b200_arith_e       arith;
+    float                 pad_value;
+    TkFloat3              mean, std_dev;      /* tk_object_detector.c:248-249                    */
+    /* detector head */
+    uint32_t              num_proposals, num_classes;    /* 25200, 80                             */
+    tk_b200_activation_e  activation;
+    float                 confidence_threshold;          /* tk_object_detector.h:55               */
+    float                 iou_threshold;                 /* tk_object_detector.h:56               */
+    uint32_t              max_candidates;     /* pre-NMS cap per frame (<= 4096); 0 = 4096       */
+    uint32_t              max_detections;     /* post-NMS cap per frame; 0 = 500 (tk_object_detector.c:39) */
+    int                   class_agnostic;
+    int                   restore_coordinates; /* 1 = boxes returned in source-frame px          */
+} tk_b200_pipeline_config_t;
+
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out_pipeline, const tk_b200_pipeline_config_t* config);
+void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pipeline);
+/* src/vision/tk_object_detector.h:166 (tk_object_detector_update_thresholds) */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_update_thresholds(tk_b200_pipeline_t* pipeline, float confidence_threshold, float iou_threshold);
+
+/* DEVICE-resident inputs and outputs; asynchronous on `stream` (3 launches).
+ * d_frames [n][frame bytes], d_logits [n][P][5+C] f32, d_tensor [n][3][H][W],
+ * d_detections [n][max_detections], d_num_detections [n]. */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_device(
+    tk_b200_pipeline_t* pipeline, const void* d_frames, const float* d_logits, uint32_t num_frames,
+    void* d_tensor, tk_b200_candidate_t* d_detections, uint32_t* d_num_detections, cudaStream_t stream);
+
+/* HOST inputs and outputs (pinned memory from tk_b200_host_alloc copies by DMA;
+ * pageable memory works, slower).  The batch is cut into chunks; upload of chunk
+ * k+1, compute of chunk k and download of chunk k-1 overlap on three streams
+ * ordered by events.  h_logits may be NULL (pre-process only) and h_frames may
+ * be NULL (post-process only).  The model-input tensors stay on the device for
+ * the detector (tk_b200_pipeline_tensor_device_ptr) and are also downloaded when
+ * h_tensor != NULL.  Blocks until the outputs are in host memory. */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_host(
+    tk_b200_pipeline_t* pipeline, const void* h_frames, const float* h_logits, uint32_t num_frames,
+    void* h_tensor, tk_b200_candidate_t* h_detections, uint32_t* h_num_detections);
+
+/* As process_host, but the logits are already on the device (where a co-located
+ * detector leaves them). */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_host_frames(
+    tk_b200_pipeline_t* pipeline, const void* h_frames, const float* d_logits, uint32_t num_frames,
+    void* h_tensor, tk_b200_candidate_t* h_detections, uint32_t* h_num_detections);
+
+/* Per-stage timing of process_device with CUDA events recorded on the caller's
+ * stream around each of the three launches: stage_timing(p, max_calls) arms it
+ * for the next max_calls calls (0 disarms); stage_times sums the recorded
+ * durations in ms — [0] pre-process, [1] decode, [2] NMS. */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_stage_timing(tk_b200_pipeline_t* pipeline, uint32_t max_calls);
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* pipeline, double ms_sum[3], uint32_t* out_calls);
+
+void*  tk_b200_pipeline_tensor_device_ptr(tk_b200_pipeline_t* pipeline);
+size_t tk_b200_pipeline_frame_bytes(const tk_b200_pipeline_t* pipeline);
+size_t tk_b200_pipeline_tensor_bytes(const tk_b200_pipeline_t* pipeline);   /* per frame */
+
+/* Single frame, reference result type: completes postprocess_detections
+ * (src/vision/tk_object_detector.c:303-368) for a HOST logit tensor
+ * [num_proposals][5+num_classes].  *out_results is malloc'd (free with
+ * tk_object_detector_free_results, src/vision/tk_object_detector.h:157); label
+ * points into class_labels (tk_object_detector.h:50-52) or is NULL. */
+TK_NODISCARD tk_error_code_t tk_b200_postprocess_detections(
+    const float* h_logits, uint32_t num_proposals, uint32_t num_classes, tk_b200_activation_e activation,
+    float confidence_threshold, float iou_threshold, uint32_t max_detections,
+    const char* const* class_labels, size_t class_count,
+    uint32_t frame_width, uint32_t frame_height, uint32_t input_width, uint32_t input_height,
+    tk_detection_result_t** out_results, size_t* out_result_count);
+
 /* Handle accessors, so tk_kernels_* launchers can run on a dispatcher's buffers
  * and compute stream. */
 void*        tk_b200_buffer_device_ptr(tk_gpu_buffer_t buffer);
@@ -203,6 +298,7 @@ void tk_b200_host_free(void* ptr);
 
 /* Library self-description (no GPU needed). */
 const char* tk_b200_version(void);
+unsigned long long tk_b200_launch_count(void);   /* kernels enqueued by this library so far */
 int tk_b200_device_count(void);
 
 #ifdef __cplusplus

@@ -170,7 +170,7 @@ uint32_t oracle_decode(const float* logits, uint32_t P, uint32_t C, float thr,
                 cls = tk_dm_expf(row[5 + best] - mx) / sum;
             }
             c->class_id = best;
-            c->confidence = obj * cls;
+            c->confidence = tk_dm_canon_nan(obj * cls);
         }
         ++total;
     }

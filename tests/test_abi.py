@@ -60,6 +60,7 @@ def test_headers_are_plain_c_and_layouts_match(tmp_path):
         "tk_b200_nms_params_t": capi.NmsParams, "tk_b200_argmax_params_t": capi.ArgmaxParams,
         "tk_b200_color_params_t": capi.ColorParams, "tk_b200_door_params_t": capi.DoorParams,
         "tk_tensor_descriptor_t": capi.TensorDescriptor, "tk_cuda_dispatcher_config_t": capi.DispatcherConfig,
+        "tk_b200_pipeline_config_t": capi.PipelineConfig,
     }
     body = "\n".join(f'    printf("{n} %zu\\n", sizeof({n}));' for n in structs)
     prog.write_text('#include <stdio.h>\n#include "tk_b200_vision.h"\nint main(void) {\n' + body +
@@ -83,6 +84,8 @@ def test_argument_validation_needs_no_gpu():
     assert lib.tk_b200_preprocess_batch(None, None) == capi.TK_ERROR_INVALID_ARGUMENT
     assert lib.tk_kernels_decode_detections(None, None) == capi.TK_ERROR_INVALID_ARGUMENT
     assert lib.tk_kernels_nms_classwise(None, None) == capi.TK_ERROR_INVALID_ARGUMENT
+    assert lib.tk_b200_pipeline_create(None, None) == capi.TK_ERROR_INVALID_ARGUMENT
+    assert lib.tk_b200_pipeline_process_host(None, None, None, 0, None, None, None) == capi.TK_ERROR_INVALID_ARGUMENT
     assert lib.tk_preprocessor_resize_and_normalize_to_chw(None, None, 0, 0, None, None) == capi.TK_ERROR_INVALID_ARGUMENT
     assert lib.tk_error_to_string(capi.TK_ERROR_INVALID_DIMENSIONS) == b"invalid dimensions"
     assert lib.tk_b200_color_name(0) == b"red" and lib.tk_b200_color_name(8) == b"gray"

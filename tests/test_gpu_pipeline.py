@@ -1,0 +1,159 @@
+"""GPU parity of the batched pipeline handle (tk_b200_pipeline_*) and of the reference-typed
+single-frame post-process, against the oracle and against the individual launchers."""
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import oracle as O
+from trackiellm_b200 import vision as V
+
+pytestmark = pytest.mark.gpu
+
+W, H = 320, 240           # small frames keep the oracle fast; full 1080p is covered in test_gpu_preprocess
+P, NC = 2000, 80
+
+
+def inputs(n, seed0=0, p=P):
+    frames = np.stack([synth.rgb_frame(W, H, seed0 + i) for i in range(n)])
+    logits = np.stack([synth.logits_tensor(seed0 + i, num_proposals=p, objects=12, dups=6, adversarial=(i == 0))
+                       for i in range(n)])
+    return frames, logits
+
+
+def oracle_dets(logit, restore=None):
+    c, _ = O.decode(logit, 0.5, cap=4096)
+    d = O.nms_classwise(c, 0.5, 500)
+    if restore:
+        d = O.restore_coords(d, *restore)
+    return d.view(V.CAND_DTYPE)
+
+
+def make_pipe(n, **kw):
+    args = dict(max_batch=n, chunk_frames=3, width=W, height=H, tensor_w=64, tensor_h=48, out_dtype=torch.float32,
+                num_proposals=P, num_classes=NC, conf_thr=0.5, iou_thr=0.5, max_detections=500)
+    args.update(kw)
+    return V.Pipeline(**args)
+
+
+def check_dets(dets, counts, logits, restore=None):
+    lists = V.candidates_to_numpy(dets if dets.is_cuda else dets.cuda(), counts if counts.is_cuda else counts.cuda())
+    for i, got in enumerate(lists):
+        ref = oracle_dets(logits[i], restore)
+        assert got.tobytes() == ref.tobytes(), f"frame {i}: {len(got)} vs {len(ref)} detections"
+
+
+def test_process_device_vs_oracle():
+    n = 7
+    frames, logits = inputs(n)
+    with make_pipe(n) as pipe:
+        t, d, c = pipe.alloc_outputs(n)
+        pipe.process_device(torch.from_numpy(frames).cuda(), torch.from_numpy(logits).cuda(), t, d, c)
+        torch.cuda.synchronize()
+        for i in range(n):
+            ref = O.preprocess_rgb8(frames[i], 64, 48)
+            assert np.array_equal(t[i].cpu().numpy().view(np.uint32), ref.view(np.uint32))
+        check_dets(d, c, logits)
+
+
+@pytest.mark.parametrize("n,chunk", [(1, 1), (7, 3), (8, 8), (10, 4), (5, 16)])
+def test_process_host_matches_oracle_and_device(n, chunk):
+    frames, logits = inputs(n, seed0=10)
+    with make_pipe(n, chunk_frames=chunk, out_dtype=torch.float16) as pipe:
+        _, hd, hc = pipe.alloc_outputs(n, pinned=True)
+        ht = torch.empty((n, 3, 48, 64), dtype=torch.float16).pin_memory()
+        hf = torch.from_numpy(frames).pin_memory()
+        hl = torch.from_numpy(logits).pin_memory()
+        for _ in range(2):                                   # twice: slot reuse across calls
+            hd.zero_(); hc.zero_(); ht.zero_()
+            pipe.process_host(hf, hl, hd, hc, tensor=ht)
+            check_dets(hd, hc, logits)
+            for i in range(n):
+                ref = O.f32_to_f16(O.preprocess_rgb8(frames[i], 64, 48)).astype(np.float32)
+                got = ht[i].numpy().astype(np.float32)
+                assert np.all(np.abs(got - ref) <= 1e-2 + 1e-2 * np.abs(ref))
+        # pageable (unpinned) host memory also works
+        hd2 = torch.zeros_like(hd); hc2 = torch.zeros_like(hc)
+        pipe.process_host(frames, logits, hd2.numpy(), hc2.numpy())
+        assert torch.equal(hd2[:, :1], hd[:, :1]) and torch.equal(hc2, hc)
+        # logits already on the device
+        hd3 = torch.zeros_like(hd).pin_memory(); hc3 = torch.zeros_like(hc).pin_memory()
+        pipe.process_host(hf, torch.from_numpy(logits).cuda(), hd3, hc3, logits_on_device=True)
+        check_dets(hd3, hc3, logits)
+
+
+def test_pre_only_and_post_only():
+    n = 4
+    frames, logits = inputs(n, seed0=20)
+    with make_pipe(n) as pipe:
+        ht = torch.zeros((n, 3, 48, 64), dtype=torch.float32).pin_memory()
+        pipe.process_host(torch.from_numpy(frames).pin_memory(), None, None, None, tensor=ht)
+        for i in range(n):
+            assert np.array_equal(ht[i].numpy().view(np.uint32), O.preprocess_rgb8(frames[i], 64, 48).view(np.uint32))
+        _, hd, hc = pipe.alloc_outputs(n, pinned=True)
+        pipe.process_host(None, torch.from_numpy(logits).pin_memory(), hd, hc)
+        check_dets(hd, hc, logits)
+
+
+def test_restore_coordinates_and_threshold_update():
+    n = 3
+    frames, logits = inputs(n, seed0=30)
+    with make_pipe(n, restore_coordinates=True) as pipe:
+        t, d, c = pipe.alloc_outputs(n)
+        pipe.process_device(torch.from_numpy(frames).cuda(), torch.from_numpy(logits).cuda(), t, d, c)
+        torch.cuda.synchronize()
+        check_dets(d, c, logits, restore=(W, H, 64, 48))
+        pipe.update_thresholds(0.7, 0.3)                      # tk_object_detector_update_thresholds
+        pipe.process_device(None, torch.from_numpy(logits).cuda(), None, d, c)
+        torch.cuda.synchronize()
+        for i, got in enumerate(V.candidates_to_numpy(d, c)):
+            cands, _ = O.decode(logits[i], 0.7, cap=4096)
+            ref = O.restore_coords(O.nms_classwise(cands, 0.3, 500), W, H, 64, 48).view(V.CAND_DTYPE)
+            assert got.tobytes() == ref.tobytes()
+
+
+def test_stage_timing_and_launch_count():
+    import ctypes as C
+    from trackiellm_b200 import _capi as capi
+    n = 4
+    frames, logits = inputs(n, seed0=40)
+    lib = capi.lib()
+    lib.tk_b200_launch_count.restype = C.c_ulonglong
+    with make_pipe(n) as pipe:
+        t, d, c = pipe.alloc_outputs(n)
+        df, dl = torch.from_numpy(frames).cuda(), torch.from_numpy(logits).cuda()
+        pipe.stage_timing(5)
+        before = lib.tk_b200_launch_count()
+        for _ in range(5):
+            pipe.process_device(df, dl, t, d, c)
+        torch.cuda.synchronize()
+        assert lib.tk_b200_launch_count() - before == 15      # pre + decode + nms per call
+        ms, calls = pipe.stage_times()
+        assert calls == 5 and all(m > 0 for m in ms)
+
+
+def test_errors():
+    with make_pipe(2) as pipe:
+        t, d, c = pipe.alloc_outputs(4)
+        fr = torch.zeros((4, H, W, 3), dtype=torch.uint8, device="cuda")
+        with pytest.raises(V.capi.TkError):                   # more frames than max_batch
+            pipe.process_device(fr, None, t, d, c)
+    with pytest.raises(V.capi.TkError):
+        make_pipe(0)
+    with pytest.raises(V.capi.TkError):
+        make_pipe(1, max_candidates=5000)
+
+
+def test_postprocess_detections_reference_result_type():
+    logit = synth.logits_tensor(5, adversarial=True)
+    labels = [f"class{i}" for i in range(80)]
+    res = V.postprocess_detections(logit, conf_thr=0.5, iou_thr=0.5, max_detections=500, class_labels=labels,
+                                   frame_wh=(1920, 1080), input_wh=(640, 640))
+    ref = oracle_dets(logit, restore=(1920, 1080, 640, 640))
+    assert len(res) == len(ref)
+    for (cid, lab, conf, box), r in zip(res, ref):
+        assert cid == r["class_id"] and lab == f"class{cid}"
+        assert np.float32(conf).tobytes() == np.float32(r["confidence"]).tobytes() or (conf != conf and r["confidence"] != r["confidence"])
+        assert box == (r["x"], r["y"], r["w"], r["h"])
+    # nothing above the threshold -> empty, NULL results
+    assert V.postprocess_detections(logit, conf_thr=2.0) == []

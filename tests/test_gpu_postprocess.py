@@ -11,7 +11,17 @@ pytestmark = pytest.mark.gpu
 
 
 def same(a, b):
-    return a.shape == b.shape and a.tobytes() == b.tobytes()
+    if a.shape != b.shape:
+        print(f"shape mismatch: {a.shape} vs {b.shape}")
+        return False
+    if a.tobytes() == b.tobytes():
+        return True
+    ab = a.view(np.uint32).reshape(len(a), -1)
+    bb = b.view(np.uint32).reshape(len(b), -1)
+    bad = np.nonzero((ab != bb).any(axis=1))[0]
+    for i in bad[:8]:
+        print(f"record {i}: gpu {a[i]} {ab[i]}  oracle {b[i]} {bb[i]}")
+    return False
 
 
 def gpu_decode(t, thr, act=V.ACT_RAW, cap=4096):
@@ -39,7 +49,7 @@ def test_decode_ragged_shapes(P, C):
     t = synth.logits_tensor(3, num_proposals=P, num_classes=C, objects=5, dups=3)
     for act in (V.ACT_RAW, V.ACT_SOFTMAX):
         c, n = gpu_decode(t, 0.25, act)
-        ref, total = O.decode(t, 0.25, act)
+        ref, total = O.decode(t, 0.25, act, cap=4096)
         assert int(n[0]) == total and same(V.candidates_to_numpy(c, n)[0], ref.view(V.CAND_DTYPE))
 
 

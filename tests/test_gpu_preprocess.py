@@ -143,3 +143,32 @@ def test_full_size_property_constant_frames():
             want = ((np.float32(v) * np.float32(1.0 / 255.0)) - np.float32(O.IMAGENET_MEAN[c])) / np.float32(O.IMAGENET_STD[c])
             plane = got[i, c]
             assert np.all(np.abs(plane - want) <= ATOL + RTOL * abs(want))
+
+
+@pytest.mark.parametrize("w,h,ow,oh,fmt", [(3840, 2160, 640, 640, "rgb"), (3840, 2160, 640, 640, "i420"),
+                                           (1920, 1080, 640, 640, "rgb"), (1280, 720, 352, 352, "rgb"),
+                                           (1000, 2000, 64, 24, "rgb")])
+def test_ring_stress_many_rows_per_cta(w, h, ow, oh, fmt):
+    """Many frames per launch -> many ring wrap-arounds per CTA (a 4K row that no output row samples
+    used to be re-armed while still in flight); repeated launches must be identical, and match the oracle."""
+    n = 12
+    if fmt == "i420":
+        fr = np.stack([synth.i420_frame(w, h, 100 + i) for i in range(n)])
+        kw = dict(width=w, height=h, fmt=V.PIXEL_I420)
+        ref_of = lambda i: O.preprocess_rgb8(O.i420_to_rgb8(fr[i], w, h), ow, oh)   # noqa: E731
+    else:
+        fr = np.stack([synth.rgb_frame(w, h, 100 + i) for i in range(n)])
+        kw = {}
+        ref_of = lambda i: O.preprocess_rgb8(fr[i], ow, oh)                         # noqa: E731
+    d = torch.from_numpy(fr).cuda()
+    first = None
+    for _ in range(6):
+        out = V.preprocess_batch(d, ow, oh, **kw)
+        torch.cuda.synchronize()
+        if first is None:
+            first = out.clone()
+        else:
+            assert torch.equal(out, first)
+    got = first.cpu().numpy()
+    for i in (0, n // 2, n - 1):
+        assert np.array_equal(bits(got[i]), bits(ref_of(i)))

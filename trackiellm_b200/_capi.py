@@ -82,7 +82,20 @@ class DecodeParams(C.Structure):           # tk_b200_decode_params_t
 class NmsParams(C.Structure):              # tk_b200_nms_params_t
     _fields_ = [("d_candidates", C.c_void_p), ("d_counts", C.c_void_p), ("num_frames", C.c_uint32),
                 ("max_candidates", C.c_uint32), ("iou_threshold", C.c_float), ("max_detections", C.c_uint32),
-                ("class_agnostic", C.c_int), ("d_detections", C.c_void_p), ("d_num_detections", C.c_void_p)]
+                ("class_agnostic", C.c_int), ("d_detections", C.c_void_p), ("d_num_detections", C.c_void_p),
+                ("restore_src_width", C.c_uint32), ("restore_src_height", C.c_uint32),
+                ("restore_in_width", C.c_uint32), ("restore_in_height", C.c_uint32)]
+
+
+class PipelineConfig(C.Structure):         # tk_b200_pipeline_config_t
+    _fields_ = [("device_id", C.c_int), ("max_batch", C.c_uint32), ("chunk_frames", C.c_uint32),
+                ("input_width", C.c_uint32), ("input_height", C.c_uint32), ("input_stride_bytes", C.c_uint32),
+                ("input_format", C.c_int), ("tensor_width", C.c_uint32), ("tensor_height", C.c_uint32),
+                ("tensor_type", C.c_int), ("resize_mode", C.c_int), ("arith", C.c_int), ("pad_value", C.c_float),
+                ("mean", TkFloat3), ("std_dev", TkFloat3), ("num_proposals", C.c_uint32), ("num_classes", C.c_uint32),
+                ("activation", C.c_int), ("confidence_threshold", C.c_float), ("iou_threshold", C.c_float),
+                ("max_candidates", C.c_uint32), ("max_detections", C.c_uint32), ("class_agnostic", C.c_int),
+                ("restore_coordinates", C.c_int)]
 
 
 class ArgmaxParams(C.Structure):           # tk_b200_argmax_params_t

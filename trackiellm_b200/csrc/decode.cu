@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const DecK k) {
                 c.bbox.y = __float2int_rz(__fsub_rn(cy, __fmul_rn(bh, 0.5f)));   // :348
                 c.bbox.w = __float2int_rz(bw);                                    // :349
                 c.bbox.h = __float2int_rz(bh);                                    // :350
-                c.confidence = __fmul_rn(obj, cls);
+                c.confidence = tk_dm_canon_nan(__fmul_rn(obj, cls));
                 c.class_id = best;
                 out[pos] = c;
             }

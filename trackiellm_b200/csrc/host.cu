@@ -260,6 +260,68 @@ extern "C" tk_error_code_t tk_classify_door_state(const tk_video_frame_t* frame,
     return *out_state_name ? TK_SUCCESS : TK_ERROR_OUT_OF_MEMORY;
 }
 
+// ---------------------------------------------------------------------------
+// postprocess_detections completed (src/vision/tk_object_detector.c:303-368):
+// HOST logits [P][5+C] -> malloc'd tk_detection_result_t[] (:359-361 is the copy
+// the reference elides), boxes restored to source-frame px (:365).  Decode and
+// NMS run on the GPU; the host only marshals the kept records into the
+// reference's result struct.
+// ---------------------------------------------------------------------------
+extern "C" tk_error_code_t tk_b200_postprocess_detections(
+    const float* h_logits, uint32_t P, uint32_t C, tk_b200_activation_e act, float conf_thr, float iou_thr,
+    uint32_t max_det, const char* const* class_labels, size_t class_count, uint32_t frame_w, uint32_t frame_h,
+    uint32_t in_w, uint32_t in_h, tk_detection_result_t** out_results, size_t* out_count) {
+    if (!h_logits || !out_results || !out_count) return TK_ERROR_INVALID_ARGUMENT;
+    *out_results = nullptr; *out_count = 0;
+    if (P == 0) return TK_ERROR_INVALID_DIMENSIONS;
+    if (max_det == 0) max_det = 500;                       // TK_OBJECT_DETECTOR_MAX_DETECTIONS, :39
+    const uint32_t cap = 4096;
+    const size_t logit_bytes = (size_t)P * (5 + (size_t)C) * sizeof(float);
+    const size_t cand_bytes = (size_t)cap * sizeof(tk_b200_candidate_t);
+    const size_t det_bytes = (size_t)max_det * sizeof(tk_b200_candidate_t);
+    HostScratch* s;
+    tk_error_code_t rc = scratch_prepare(&s);
+    if (rc != TK_SUCCESS) return rc;
+    if ((rc = scratch_reserve(s, 0, logit_bytes)) != TK_SUCCESS) return rc;
+    if ((rc = scratch_reserve(s, 1, cand_bytes + det_bytes + 512)) != TK_SUCCESS) return rc;
+    uint8_t* base = static_cast<uint8_t*>(s->buf[1]);
+    tk_b200_candidate_t* d_c = reinterpret_cast<tk_b200_candidate_t*>(base);
+    const size_t off_d = (cand_bytes + 255) & ~(size_t)255;
+    tk_b200_candidate_t* d_d = reinterpret_cast<tk_b200_candidate_t*>(base + off_d);
+    uint32_t* d_n = reinterpret_cast<uint32_t*>(base + ((off_d + det_bytes + 255) & ~(size_t)255));
+    TK_CUDA_TRY(cudaMemcpyAsync(s->buf[0], h_logits, logit_bytes, cudaMemcpyHostToDevice, s->stream), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    tk_b200_decode_params_t d{};
+    d.d_logits = static_cast<const float*>(s->buf[0]); d.num_frames = 1; d.num_proposals = P; d.num_classes = C;
+    d.confidence_threshold = conf_thr; d.activation = act; d.d_candidates = d_c; d.d_counts = d_n; d.max_candidates = cap;
+    if ((rc = tk_kernels_decode_detections(&d, s->stream)) != TK_SUCCESS) return rc;
+    tk_b200_nms_params_t m{};
+    m.d_candidates = d_c; m.d_counts = d_n; m.num_frames = 1; m.max_candidates = cap; m.iou_threshold = iou_thr;
+    m.max_detections = max_det; m.class_agnostic = 0; m.d_detections = d_d; m.d_num_detections = d_n + 1;
+    if (frame_w && frame_h && in_w && in_h) {
+        m.restore_src_width = frame_w; m.restore_src_height = frame_h; m.restore_in_width = in_w; m.restore_in_height = in_h;
+    }
+    if ((rc = tk_kernels_nms_classwise(&m, s->stream)) != TK_SUCCESS) return rc;
+    uint32_t n = 0;
+    TK_CUDA_TRY(cudaMemcpyAsync(&n, d_n + 1, 4, cudaMemcpyDeviceToHost, s->stream), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    TK_CUDA_TRY(cudaStreamSynchronize(s->stream), TK_ERROR_CUDA_KERNEL_FAILURE);
+    if (n == 0) return TK_SUCCESS;
+    tk_b200_candidate_t* tmp = static_cast<tk_b200_candidate_t*>(malloc((size_t)n * sizeof(tk_b200_candidate_t)));
+    tk_detection_result_t* res = static_cast<tk_detection_result_t*>(calloc(n, sizeof(tk_detection_result_t)));
+    if (!tmp || !res) { free(tmp); free(res); return TK_ERROR_OUT_OF_MEMORY; }
+    if (cudaMemcpy(tmp, d_d, (size_t)n * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError(); free(tmp); free(res); return TK_ERROR_GPU_MEMORY_COPY_FAILED;
+    }
+    for (uint32_t i = 0; i < n; ++i) {
+        res[i].class_id = tmp[i].class_id;
+        res[i].label = (class_labels && tmp[i].class_id < class_count) ? class_labels[tmp[i].class_id] : nullptr;
+        res[i].confidence = tmp[i].confidence;
+        res[i].bbox = tmp[i].bbox;
+    }
+    free(tmp);
+    *out_results = res; *out_count = n;
+    return TK_SUCCESS;
+}
+
 // src/vision/tk_object_detector.c:205-210
 extern "C" void tk_object_detector_free_results(tk_detection_result_t** results) {
     if (results && *results) { free(*results); *results = nullptr; }

@@ -37,6 +37,8 @@ struct NmsK {
     uint32_t cap, max_det, Kp;      // Kp: power of two >= cap (>= 64)
     float thr;
     int agnostic;
+    int restore;
+    float sx, sy;                   // src/in scale of the optional coordinate restore
 };
 
 // src/vision/src/object_analysis.rs:71-91 (i32 arithmetic wraps like release-mode Rust).
@@ -164,7 +166,16 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
 #pragma unroll
         for (int w = 0; w < kNmsWarps; ++w) { uint32_t t = warp_tot[w]; before += (uint32_t)w < warp ? t : 0u; tot += t; }
         const uint32_t o = run + before + __popc(bal & ((1u << lane) - 1u));
-        if (keep && o < k.max_det) out[o] = in[pos[i]];
+        if (keep && o < k.max_det) {
+            tk_b200_candidate_t c = in[pos[i]];
+            if (k.restore) {
+                c.bbox.x = __float2int_rz(__fmul_rn((float)c.bbox.x, k.sx));
+                c.bbox.y = __float2int_rz(__fmul_rn((float)c.bbox.y, k.sy));
+                c.bbox.w = __float2int_rz(__fmul_rn((float)c.bbox.w, k.sx));
+                c.bbox.h = __float2int_rz(__fmul_rn((float)c.bbox.h, k.sy));
+            }
+            out[o] = c;
+        }
         run += tot;
         __syncthreads();
         if (run >= k.max_det) break;
@@ -193,6 +204,14 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
     k.cap = p->max_candidates; k.max_det = p->max_detections;
     k.Kp = 64; while (k.Kp < k.cap) k.Kp <<= 1;
     k.thr = p->iou_threshold; k.agnostic = p->class_agnostic;
+    const bool any_restore = p->restore_src_width || p->restore_src_height || p->restore_in_width || p->restore_in_height;
+    if (any_restore) {
+        if (!p->restore_src_width || !p->restore_src_height || !p->restore_in_width || !p->restore_in_height)
+            return TK_ERROR_INVALID_DIMENSIONS;
+        k.restore = 1;
+        k.sx = (float)p->restore_src_width / (float)p->restore_in_width;
+        k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
+    }
     const size_t smem = (size_t)k.Kp * (8 + 16 + 4 + 4 + 1);
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);

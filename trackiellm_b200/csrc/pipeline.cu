@@ -1,0 +1,348 @@
+// pipeline.cu — batched pre-process + decode + class-wise NMS behind one handle.
+//
+// The reference runs this path one frame per call inside
+// tk_object_detector_detect (src/vision/tk_object_detector.c:182-203:
+// preprocess_frame :223-259 with a synchronous pageable cudaMemcpy :229,
+// postprocess_detections :303-368).  Here a batch of frames of one geometry goes
+// through three launches (preprocess_kernel, decode_kernel, nms_kernel), and the
+// host-buffer form cuts the batch into chunks so that the upload of chunk k+1,
+// the kernels of chunk k and the download of chunk k-1 overlap on three streams
+// ordered by events (the reference's dispatcher creates three streams and never
+// orders them, src/gpu/cuda/tk_cuda_dispatch.cu:107-137).
+//
+// Nothing here computes on the CPU.
+#include "tk_common.cuh"
+
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+
+namespace tkb {
+
+static constexpr int kSlots = 3;            // in-flight chunks of process_host
+
+struct DevScope {
+    int prev = -1; bool ok = false;
+    explicit DevScope(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+        ok = cudaSetDevice(dev) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+    }
+    ~DevScope() { if (prev >= 0 ) cudaSetDevice(prev); }
+};
+
+}  // namespace tkb
+
+struct tk_b200_pipeline_s {
+    tk_b200_pipeline_config_t cfg;
+    size_t frame_bytes, logit_bytes, tensor_bytes;     // per frame
+    uint32_t chunk;
+    cudaStream_t s_up, s_compute, s_down;
+    cudaEvent_t ev_uploaded[tkb::kSlots], ev_computed[tkb::kSlots], ev_downloaded[tkb::kSlots];
+    uint8_t* d_frames[tkb::kSlots];                    // [chunk][frame_bytes (+ slack)]
+    float*   d_logits[tkb::kSlots];                    // [chunk][P][5+C]
+    uint8_t* d_tensor;                                 // [max_batch][tensor_bytes]
+    tk_b200_candidate_t* d_cands;                      // [max_batch][max_candidates]
+    uint32_t* d_counts;                                // [max_batch]
+    tk_b200_candidate_t* d_dets;                       // [max_batch][max_detections]
+    uint32_t* d_ndets;                                 // [max_batch]
+    // Optional per-stage timing of process_device: 4 events per call (before pre,
+    // after pre, after decode, after nms) on the caller's stream.
+    int timing_on;
+    uint32_t timing_calls, timing_cap;
+    cudaEvent_t* timing_ev;                            // [timing_cap][4]
+};
+
+using namespace tkb;
+
+static size_t frame_bytes_of(const tk_b200_pipeline_config_t& c) {
+    uint32_t bpp = c.input_format == TK_PIXEL_FORMAT_RGB8 ? 3 : (c.input_format == TK_PIXEL_FORMAT_RGBA8 ? 4 : 1);
+    size_t stride = c.input_stride_bytes ? c.input_stride_bytes : (size_t)c.input_width * bpp;
+    size_t b = stride * c.input_height;
+    if (c.input_format == TK_PIXEL_FORMAT_I420) b += 2 * (stride / 2) * (size_t)(c.input_height / 2);
+    return b;
+}
+
+extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
+    if (!pp || !*pp) return;
+    tk_b200_pipeline_t* p = *pp;
+    {
+        DevScope scope(p->cfg.device_id);
+        if (p->s_up) { cudaStreamSynchronize(p->s_up); }
+        if (p->s_compute) { cudaStreamSynchronize(p->s_compute); }
+        if (p->s_down) { cudaStreamSynchronize(p->s_down); }
+        for (int i = 0; i < kSlots; ++i) {
+            if (p->d_frames[i]) cudaFree(p->d_frames[i]);
+            if (p->d_logits[i]) cudaFree(p->d_logits[i]);
+            if (p->ev_uploaded[i]) cudaEventDestroy(p->ev_uploaded[i]);
+            if (p->ev_computed[i]) cudaEventDestroy(p->ev_computed[i]);
+            if (p->ev_downloaded[i]) cudaEventDestroy(p->ev_downloaded[i]);
+        }
+        if (p->d_tensor) cudaFree(p->d_tensor);
+        if (p->d_cands) cudaFree(p->d_cands);
+        if (p->d_counts) cudaFree(p->d_counts);
+        if (p->d_dets) cudaFree(p->d_dets);
+        if (p->d_ndets) cudaFree(p->d_ndets);
+        for (uint32_t i = 0; p->timing_ev && i < p->timing_cap * 4; ++i) if (p->timing_ev[i]) cudaEventDestroy(p->timing_ev[i]);
+        free(p->timing_ev);
+        if (p->s_up) cudaStreamDestroy(p->s_up);
+        if (p->s_compute) cudaStreamDestroy(p->s_compute);
+        if (p->s_down) cudaStreamDestroy(p->s_down);
+        cudaGetLastError();
+    }
+    delete p;
+    *pp = nullptr;
+}
+
+extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, const tk_b200_pipeline_config_t* cfg) {
+    if (!out || !cfg) return TK_ERROR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if (cfg->max_batch == 0) return TK_ERROR_INVALID_ARGUMENT;
+    if (cfg->input_width < 2 || cfg->input_height < 2 || cfg->tensor_width == 0 || cfg->tensor_height == 0)
+        return TK_ERROR_INVALID_DIMENSIONS;
+    if (cfg->input_format != TK_PIXEL_FORMAT_RGB8 && cfg->input_format != TK_PIXEL_FORMAT_RGBA8 &&
+        cfg->input_format != TK_PIXEL_FORMAT_I420)
+        return TK_ERROR_INVALID_ARGUMENT;
+    if (cfg->max_candidates > 4096) return TK_ERROR_INVALID_ARGUMENT;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return TK_ERROR_GPU_DEVICE_ENUMERATION_FAILED; }
+    if (count == 0 || cfg->device_id < 0 || cfg->device_id >= count) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
+    DevScope scope(cfg->device_id);
+    if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    if (!device_info()) return TK_ERROR_GPU_DEVICE_UNSUPPORTED;
+
+    tk_b200_pipeline_t* p = new (std::nothrow) tk_b200_pipeline_t();
+    if (!p) return TK_ERROR_OUT_OF_MEMORY;
+    p->cfg = *cfg;
+    if (p->cfg.max_candidates == 0) p->cfg.max_candidates = 4096;
+    if (p->cfg.max_detections == 0) p->cfg.max_detections = 500;      // TK_OBJECT_DETECTOR_MAX_DETECTIONS, tk_object_detector.c:39
+    p->chunk = cfg->chunk_frames ? cfg->chunk_frames : 8;
+    if (p->chunk > cfg->max_batch) p->chunk = cfg->max_batch;
+    p->frame_bytes = frame_bytes_of(*cfg);
+    p->logit_bytes = (size_t)cfg->num_proposals * (5 + (size_t)cfg->num_classes) * sizeof(float);
+    p->tensor_bytes = (size_t)cfg->tensor_width * cfg->tensor_height * 3 * (cfg->tensor_type == TK_B200_OUT_F16 ? 2 : 4);
+
+    bool ok = cudaStreamCreateWithFlags(&p->s_up, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_compute, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_down, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < kSlots; ++i) {
+        ok = cudaEventCreateWithFlags(&p->ev_uploaded[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&p->ev_computed[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&p->ev_downloaded[i], cudaEventDisableTiming) == cudaSuccess;
+    }
+    if (!ok) { cudaGetLastError(); tk_b200_pipeline_destroy(&p); return TK_ERROR_GPU_STREAM_CREATION_FAILED; }
+
+    const size_t mb = cfg->max_batch;
+    // +64 B: the row ring's 16-byte bulk copies may run past the last row of the last frame.
+    for (int i = 0; ok && i < kSlots; ++i) {
+        ok = cudaMalloc(reinterpret_cast<void**>(&p->d_frames[i]), p->chunk * p->frame_bytes + 64) == cudaSuccess;
+        if (ok && p->logit_bytes) ok = cudaMalloc(reinterpret_cast<void**>(&p->d_logits[i]), p->chunk * p->logit_bytes) == cudaSuccess;
+    }
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_tensor), mb * p->tensor_bytes) == cudaSuccess;
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_cands), mb * p->cfg.max_candidates * sizeof(tk_b200_candidate_t)) == cudaSuccess;
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_counts), mb * sizeof(uint32_t)) == cudaSuccess;
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_dets), mb * p->cfg.max_detections * sizeof(tk_b200_candidate_t)) == cudaSuccess;
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_ndets), mb * sizeof(uint32_t)) == cudaSuccess;
+    if (!ok) {
+        tk_error_set_detail("pipeline buffers: %s", cudaGetErrorString(cudaGetLastError()));
+        tk_b200_pipeline_destroy(&p);
+        return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
+    }
+    *out = p;
+    return TK_SUCCESS;
+}
+
+// src/vision/tk_object_detector.c:212-219
+extern "C" tk_error_code_t tk_b200_pipeline_update_thresholds(tk_b200_pipeline_t* p, float conf, float iou) {
+    if (!p) return TK_ERROR_INVALID_ARGUMENT;
+    p->cfg.confidence_threshold = conf;
+    p->cfg.iou_threshold = iou;
+    return TK_SUCCESS;
+}
+
+extern "C" void* tk_b200_pipeline_tensor_device_ptr(tk_b200_pipeline_t* p) { return p ? p->d_tensor : nullptr; }
+extern "C" size_t tk_b200_pipeline_frame_bytes(const tk_b200_pipeline_t* p) { return p ? p->frame_bytes : 0; }
+extern "C" size_t tk_b200_pipeline_tensor_bytes(const tk_b200_pipeline_t* p) { return p ? p->tensor_bytes : 0; }
+
+// The three launches for `n` frames whose inputs are in HBM.
+static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits, uint32_t n,
+                                   void* d_tensor, tk_b200_candidate_t* d_cands, uint32_t* d_counts,
+                                   tk_b200_candidate_t* d_dets, uint32_t* d_ndets, cudaStream_t st,
+                                   cudaEvent_t* tev = nullptr) {
+    const tk_b200_pipeline_config_t& c = p->cfg;
+    tk_error_code_t rc;
+    if (tev) cudaEventRecord(tev[0], st);
+    if (d_frames) {
+        if (!d_tensor) return TK_ERROR_INVALID_ARGUMENT;
+        tk_b200_preprocess_batch_params_t b{};
+        b.d_input = d_frames; b.input_frame_pitch_bytes = p->frame_bytes; b.num_frames = n;
+        b.input_width = c.input_width; b.input_height = c.input_height; b.input_stride_bytes = c.input_stride_bytes;
+        b.input_format = c.input_format;
+        b.d_output = d_tensor; b.output_width = c.tensor_width; b.output_height = c.tensor_height;
+        b.output_type = c.tensor_type; b.resize_mode = c.resize_mode; b.pad_value = c.pad_value; b.arith = c.arith;
+        b.mean = c.mean; b.std_dev = c.std_dev;
+        if ((rc = tk_b200_preprocess_batch(&b, st)) != TK_SUCCESS) return rc;
+    }
+    if (tev) cudaEventRecord(tev[1], st);
+    if (d_logits) {
+        if (!d_dets || !d_ndets) return TK_ERROR_INVALID_ARGUMENT;
+        tk_b200_decode_params_t d{};
+        d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
+        d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
+        d.d_candidates = d_cands; d.d_counts = d_counts; d.max_candidates = c.max_candidates;
+        if ((rc = tk_kernels_decode_detections(&d, st)) != TK_SUCCESS) return rc;
+        if (tev) cudaEventRecord(tev[2], st);
+        tk_b200_nms_params_t m{};
+        m.d_candidates = d_cands; m.d_counts = d_counts; m.num_frames = n; m.max_candidates = c.max_candidates;
+        m.iou_threshold = c.iou_threshold; m.max_detections = c.max_detections; m.class_agnostic = c.class_agnostic;
+        m.d_detections = d_dets; m.d_num_detections = d_ndets;
+        if (c.restore_coordinates) {
+            // Stretch inverse; a letterboxed tensor would also need the pad offsets, which
+            // the reference never defines (convert_to_original_coordinates is empty).
+            if (c.resize_mode != TK_B200_RESIZE_STRETCH) return TK_ERROR_NOT_IMPLEMENTED;
+            m.restore_src_width = c.input_width; m.restore_src_height = c.input_height;
+            m.restore_in_width = c.tensor_width; m.restore_in_height = c.tensor_height;
+        }
+        if ((rc = tk_kernels_nms_classwise(&m, st)) != TK_SUCCESS) return rc;
+    } else if (tev) {
+        cudaEventRecord(tev[2], st);
+    }
+    if (tev) cudaEventRecord(tev[3], st);
+    return TK_SUCCESS;
+}
+
+extern "C" tk_error_code_t tk_b200_pipeline_process_device(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits,
+                                                           uint32_t n, void* d_tensor, tk_b200_candidate_t* d_dets,
+                                                           uint32_t* d_ndets, cudaStream_t stream) {
+    if (!p || (!d_frames && !d_logits)) return TK_ERROR_INVALID_ARGUMENT;
+    if (n == 0) return TK_SUCCESS;
+    if (n > p->cfg.max_batch) return TK_ERROR_BUFFER_TOO_SMALL;
+    DevScope scope(p->cfg.device_id);
+    if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    cudaEvent_t* tev = nullptr;
+    if (p->timing_on && p->timing_calls < p->timing_cap) tev = p->timing_ev + 4 * (size_t)p->timing_calls++;
+    return run_kernels(p, d_frames, d_logits, n, d_tensor, p->d_cands, p->d_counts, d_dets, d_ndets, stream, tev);
+}
+
+// Stage timing of process_device with CUDA events on the caller's stream.
+// enable(max_calls > 0) arms it for the next max_calls calls; enable(0) disarms.
+extern "C" tk_error_code_t tk_b200_pipeline_stage_timing(tk_b200_pipeline_t* p, uint32_t max_calls) {
+    if (!p) return TK_ERROR_INVALID_ARGUMENT;
+    DevScope scope(p->cfg.device_id);
+    if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    p->timing_on = 0; p->timing_calls = 0;
+    if (max_calls == 0) return TK_SUCCESS;
+    if (max_calls > p->timing_cap) {
+        cudaEvent_t* ev = static_cast<cudaEvent_t*>(calloc((size_t)max_calls * 4, sizeof(cudaEvent_t)));
+        if (!ev) return TK_ERROR_OUT_OF_MEMORY;
+        for (uint32_t i = 0; i < max_calls * 4; ++i) {
+            if (i < p->timing_cap * 4) ev[i] = p->timing_ev[i];
+            else if (cudaEventCreate(&ev[i]) != cudaSuccess) { cudaGetLastError(); free(ev); return TK_ERROR_GPU_CUDA_ERROR; }
+        }
+        free(p->timing_ev);
+        p->timing_ev = ev; p->timing_cap = max_calls;
+    }
+    p->timing_on = 1;
+    return TK_SUCCESS;
+}
+
+// Sums of the recorded stage durations (ms): [0] pre-process, [1] decode, [2] NMS;
+// *out_calls = calls recorded.  Waits for the recorded events to complete.
+extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, double ms_sum[3], uint32_t* out_calls) {
+    if (!p || !ms_sum || !out_calls) return TK_ERROR_INVALID_ARGUMENT;
+    DevScope scope(p->cfg.device_id);
+    if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    ms_sum[0] = ms_sum[1] = ms_sum[2] = 0.0;
+    *out_calls = p->timing_calls;
+    for (uint32_t c = 0; c < p->timing_calls; ++c) {
+        cudaEvent_t* e = p->timing_ev + 4 * (size_t)c;
+        TK_CUDA_TRY(cudaEventSynchronize(e[3]), TK_ERROR_GPU_SYNCHRONIZATION_FAILED);
+        for (int s = 0; s < 3; ++s) {
+            float ms = 0.0f;
+            TK_CUDA_TRY(cudaEventElapsedTime(&ms, e[s], e[s + 1]), TK_ERROR_GPU_CUDA_ERROR);
+            ms_sum[s] += (double)ms;
+        }
+    }
+    return TK_SUCCESS;
+}
+
+#define TK_PIPE_TRY(call) TK_CUDA_TRY(call, TK_ERROR_GPU_MEMORY_COPY_FAILED)
+
+// Chunked three-stream flow.  Slot s = chunk % kSlots owns one frame buffer, one
+// logit buffer and three events:
+//   upload(k)   waits computed(k - kSlots)   (the slot's previous kernels are done reading)
+//   compute(k)  waits uploaded(k)
+//   download(k) waits computed(k)
+// Outputs (tensor, detections, counts) have per-frame homes for the whole batch,
+// so downloads never block later compute.
+static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_frames, const float* h_logits,
+                                         const float* d_logits_all, uint32_t n, void* h_tensor,
+                                         tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
+    if (!p) return TK_ERROR_INVALID_ARGUMENT;
+    const bool have_logits = h_logits || d_logits_all;
+    if (!h_frames && !have_logits) return TK_ERROR_INVALID_ARGUMENT;
+    if (have_logits && (!h_dets || !h_ndets)) return TK_ERROR_INVALID_ARGUMENT;
+    if (have_logits && p->logit_bytes == 0) return TK_ERROR_INVALID_DIMENSIONS;
+    if (n == 0) return TK_SUCCESS;
+    if (n > p->cfg.max_batch) return TK_ERROR_BUFFER_TOO_SMALL;
+    DevScope scope(p->cfg.device_id);
+    if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    const size_t det_stride = p->cfg.max_detections;
+    const uint32_t chunks = (n + p->chunk - 1) / p->chunk;
+    tk_error_code_t rc = TK_SUCCESS;
+    for (uint32_t k = 0; k < chunks && rc == TK_SUCCESS; ++k) {
+        const int s = (int)(k % kSlots);
+        const uint32_t f0 = k * p->chunk;
+        const uint32_t m = (n - f0) < p->chunk ? (n - f0) : p->chunk;
+        // ---- upload
+        if (k >= (uint32_t)kSlots) TK_PIPE_TRY(cudaStreamWaitEvent(p->s_up, p->ev_computed[s], 0));
+        if (h_frames)
+            TK_PIPE_TRY(cudaMemcpyAsync(p->d_frames[s], static_cast<const uint8_t*>(h_frames) + (size_t)f0 * p->frame_bytes,
+                                        (size_t)m * p->frame_bytes, cudaMemcpyHostToDevice, p->s_up));
+        if (h_logits)
+            TK_PIPE_TRY(cudaMemcpyAsync(p->d_logits[s], reinterpret_cast<const uint8_t*>(h_logits) + (size_t)f0 * p->logit_bytes,
+                                        (size_t)m * p->logit_bytes, cudaMemcpyHostToDevice, p->s_up));
+        TK_PIPE_TRY(cudaEventRecord(p->ev_uploaded[s], p->s_up));
+        // ---- compute
+        TK_PIPE_TRY(cudaStreamWaitEvent(p->s_compute, p->ev_uploaded[s], 0));
+        const float* dl = h_logits ? p->d_logits[s]
+                                   : (d_logits_all ? reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(d_logits_all) + (size_t)f0 * p->logit_bytes)
+                                                   : nullptr);
+        rc = run_kernels(p, h_frames ? p->d_frames[s] : nullptr, dl, m, p->d_tensor + (size_t)f0 * p->tensor_bytes,
+                         p->d_cands + (size_t)f0 * p->cfg.max_candidates, p->d_counts + f0,
+                         p->d_dets + (size_t)f0 * det_stride, p->d_ndets + f0, p->s_compute);
+        if (rc != TK_SUCCESS) break;
+        TK_PIPE_TRY(cudaEventRecord(p->ev_computed[s], p->s_compute));
+        // ---- download
+        TK_PIPE_TRY(cudaStreamWaitEvent(p->s_down, p->ev_computed[s], 0));
+        if (have_logits) {
+            TK_PIPE_TRY(cudaMemcpyAsync(h_dets + (size_t)f0 * det_stride, p->d_dets + (size_t)f0 * det_stride,
+                                        (size_t)m * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_down));
+            TK_PIPE_TRY(cudaMemcpyAsync(h_ndets + f0, p->d_ndets + f0, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_down));
+        }
+        if (h_tensor && h_frames)
+            TK_PIPE_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h_tensor) + (size_t)f0 * p->tensor_bytes,
+                                        p->d_tensor + (size_t)f0 * p->tensor_bytes, (size_t)m * p->tensor_bytes,
+                                        cudaMemcpyDeviceToHost, p->s_down));
+    }
+    // Drain even after an error so no copy is left in flight on the caller's buffers.
+    cudaError_t e1 = cudaStreamSynchronize(p->s_up), e2 = cudaStreamSynchronize(p->s_compute), e3 = cudaStreamSynchronize(p->s_down);
+    if (rc == TK_SUCCESS && (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess)) {
+        cudaError_t e = e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3);
+        tk_error_set_detail("pipeline drain: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        rc = TK_ERROR_CUDA_KERNEL_FAILURE;
+    }
+    return rc;
+}
+
+extern "C" tk_error_code_t tk_b200_pipeline_process_host(tk_b200_pipeline_t* p, const void* h_frames, const float* h_logits,
+                                                         uint32_t n, void* h_tensor, tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
+    return process_host_impl(p, h_frames, h_logits, nullptr, n, h_tensor, h_dets, h_ndets);
+}
+
+extern "C" tk_error_code_t tk_b200_pipeline_process_host_frames(tk_b200_pipeline_t* p, const void* h_frames, const float* d_logits,
+                                                                uint32_t n, void* h_tensor, tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
+    if (!h_frames) return TK_ERROR_INVALID_ARGUMENT;
+    return process_host_impl(p, h_frames, nullptr, d_logits, n, h_tensor, h_dets, h_ndets);
+}

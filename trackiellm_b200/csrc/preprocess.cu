@@ -46,6 +46,7 @@ struct PreK {
     uint32_t ring_off;      // byte offset of the ring in dynamic smem
     uint32_t group_rows;    // output rows per consumer group
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
+    uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
 };
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
@@ -141,16 +142,22 @@ __device__ __forceinline__ float norm_only(const PreK& p, int c, float v) {
     }
 }
 
-// Inside-region output rows [a, b) of an item covering output rows [h0, h1).
-__device__ __forceinline__ void item_src_rows(const PreK& p, uint32_t h0, uint32_t h1, int& ylo, int& nrows) {
+// Source row of output row h (src/vision/tk_image_preprocessor.c:49,51), clamped so row+1 exists.
+__device__ __forceinline__ int src_row_of(const PreK& p, uint32_t h) {
+    return min(__float2int_rz(__fmul_rn(p.y_ratio, (float)(h - p.pad_top))), (int)p.src_h - 2);
+}
+
+// Inside-region output rows [a, b) of an item covering output rows [h0, h1), and the
+// ring sequence the item occupies:
+//   dense  (y_ratio < 2): every source row ylo .. y(b-1)+1 once, seq = row - ylo;
+//   sparse (y_ratio >= 2): rows y(h), y(h)+1 per output row, seq = 2*(h - a) + {0,1} —
+//          source rows no output row samples are never fetched.
+__device__ __forceinline__ void item_src_rows(const PreK& p, uint32_t h0, uint32_t h1, int& ylo, int& nrows, uint32_t& a_out) {
     uint32_t a = max(h0, p.pad_top), b = min(h1, p.pad_top + p.new_h);
+    a_out = a;
     if (a >= b) { ylo = 0; nrows = 0; return; }
-    int y_first = __float2int_rz(__fmul_rn(p.y_ratio, (float)(a - p.pad_top)));
-    int y_last = __float2int_rz(__fmul_rn(p.y_ratio, (float)(b - 1 - p.pad_top)));
-    y_first = min(y_first, (int)p.src_h - 2);
-    y_last = min(y_last, (int)p.src_h - 2);
-    ylo = y_first;
-    nrows = y_last + 1 - y_first + 1;
+    ylo = src_row_of(p, a);
+    nrows = p.sparse ? (int)(2u * (b - a)) : src_row_of(p, b - 1) + 2 - ylo;
 }
 
 template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
@@ -203,14 +210,19 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
 
     // ---- producer cursor (uniform across threads; only tid 0 issues TMA) ----
     uint32_t pf = f_first, p_seq = 0;
-    int p_row = 0, p_end = -1;           // next source row to stage, last row of the item
+    int p_row = 0, p_end = -1;           // dense: next source row to stage, last row of the item
+    uint32_t p_h = 0, p_hend = 0, p_k = 0;   // sparse: output row being staged, end row, 0/1 = top/bottom source row
     bool p_valid = false;
     const uint8_t* p_base = nullptr;
     auto producer_seek = [&]() {         // position on the next item that needs source rows
         while (pf <= f_last) {
-            uint32_t h0, h1; item_rows(pf, h0, h1);
-            int ylo, n; item_src_rows(p, h0, h1, ylo, n);
-            if (n > 0) { p_row = ylo; p_end = ylo + n - 1; p_base = frame_ptr(pf); p_valid = true; return; }
+            uint32_t h0, h1, a; item_rows(pf, h0, h1);
+            int ylo, n; item_src_rows(p, h0, h1, ylo, n, a);
+            if (n > 0) {
+                p_row = ylo; p_end = ylo + n - 1;
+                p_h = a; p_hend = a + (uint32_t)n / 2; p_k = 0;
+                p_base = frame_ptr(pf); p_valid = true; return;
+            }
             ++pf;
         }
         p_valid = false;
@@ -223,6 +235,9 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
         const uint8_t* src = base + (size_t)row * p.src_stride;
         if constexpr (TMA) {
             if (tid == 0) {
+                // The slot's previous copy must have landed before its barrier is re-armed
+                // (a row no consumer waited on may still be in flight).
+                if (seq >= S) mbar_wait(&bars[slot], ((seq >> p.s_log2) - 1u) & 1u);
                 if constexpr (FMT == FMT_I420) {
                     uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
                     mbar_arrive_expect_tx(&bars[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
@@ -251,9 +266,15 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
     auto produce = [&](uint32_t limit_seq) {
         if (TMA && tid == 0) fence_proxy_async();
         while (p_valid && (int32_t)(p_seq - limit_seq) < 0) {
-            stage_row(p_seq, p_base, p_row);
-            ++p_seq;
-            if (++p_row > p_end) { ++pf; producer_seek(); }
+            if (p.sparse) {
+                stage_row(p_seq, p_base, src_row_of(p, p_h) + (int)p_k);
+                ++p_seq;
+                if (++p_k == 2) { p_k = 0; if (++p_h >= p_hend) { ++pf; producer_seek(); } }
+            } else {
+                stage_row(p_seq, p_base, p_row);
+                ++p_seq;
+                if (++p_row > p_end) { ++pf; producer_seek(); }
+            }
         }
     };
 
@@ -268,7 +289,7 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
 
     for (uint32_t f = f_first; f <= f_last; ++f) {
         uint32_t h0, h1; item_rows(f, h0, h1);
-        int ylo, nrows; item_src_rows(p, h0, h1, ylo, nrows);
+        int ylo, nrows; uint32_t a_first; item_src_rows(p, h0, h1, ylo, nrows, a_first);
         for (uint32_t hg = h0; hg < h1; hg += p.group_rows) {
             const uint32_t hge = min(hg + p.group_rows, h1);
             // First source row this group still needs -> how far the producer may run.
@@ -276,8 +297,7 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
             {
                 uint32_t a = max(hg, p.pad_top), b = min(hge, p.pad_top + p.new_h);
                 if (a < b) {
-                    int y = min(__float2int_rz(__fmul_rn(p.y_ratio, (float)(a - p.pad_top))), (int)p.src_h - 2);
-                    need_seq = seq_base + (uint32_t)(y - ylo);
+                    need_seq = seq_base + (p.sparse ? 2u * (a - a_first) : (uint32_t)(src_row_of(p, a) - ylo));
                 } else if (hg >= p.pad_top + p.new_h) {
                     need_seq = seq_base + (uint32_t)nrows;
                 }
@@ -295,7 +315,7 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
                     int y = min(__float2int_rz(gy), (int)p.src_h - 2);
                     yd = __fsub_rn(gy, (float)y);
                     omy = __fsub_rn(1.0f, yd);
-                    uint32_t q0 = seq_base + (uint32_t)(y - ylo), q1 = q0 + 1;
+                    uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
                     row0 = ring + (size_t)(q0 & smask) * p.slot_bytes;
                     row1 = ring + (size_t)(q1 & smask) * p.slot_bytes;
                     if (TMA) {
@@ -510,20 +530,28 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     dim3 block(tx, ty);
 
     // Ring depth: largest power of two that fits the budget; two CTAs per SM when possible.
-    auto span_rows = [&](uint32_t g) { return (uint32_t)((double)(g - 1) * (double)k.y_ratio) + 3; };
-    uint32_t group = ty * 2;
-    size_t budget = 100 * 1024;
-    uint32_t s_log2 = 0;
-    for (int attempt = 0; attempt < 4; ++attempt) {
-        size_t avail = budget > k.ring_off ? budget - k.ring_off : 0;
-        uint32_t slots = (uint32_t)(avail / slot);
-        s_log2 = 0;
-        while ((2u << s_log2) <= slots && s_log2 < 6) ++s_log2;
-        if (slots >= 2 && (1u << s_log2) >= span_rows(group) + 1) break;
-        if (attempt == 0) { group = ty; }
-        else if (attempt == 1) { budget = (size_t)dev->max_smem_optin; group = ty * 2; }
-        else if (attempt == 2) { group = ty; }
-        else { tk_error_set_detail("source rows of %u bytes do not fit the shared-memory ring", slot); return TK_ERROR_NOT_IMPLEMENTED; }
+    k.sparse = k.y_ratio >= 2.0f ? 1u : 0u;
+    auto span_rows = [&](uint32_t g) { return k.sparse ? 2u * g : (uint32_t)((double)(g - 1) * (double)k.y_ratio) + 3; };
+    // Output rows per consumer group: as many as the ring can cover (an extreme
+    // vertical downscale spans many source rows per output row, so the group
+    // shrinks, down to a single row), first within the two-CTAs-per-SM budget.
+    uint32_t group = 0, s_log2 = 0;
+    const size_t budgets[2] = {100 * 1024, (size_t)dev->max_smem_optin};
+    for (int bi = 0; bi < 2 && !group; ++bi) {
+        const size_t avail = budgets[bi] > k.ring_off ? budgets[bi] - k.ring_off : 0;
+        const uint32_t slots = (uint32_t)(avail / slot);
+        uint32_t lg = 0;
+        while ((2u << lg) <= slots && lg < 6) ++lg;
+        if (slots < 2) continue;
+        for (uint32_t g = ty * 2; g >= 1; g = (g > ty ? ty : g / 2)) {
+            const uint32_t gg = g < k.dst_h ? g : k.dst_h;
+            if ((1u << lg) >= span_rows(gg) + 1) { group = gg; s_log2 = lg; break; }
+            if (g == 1) break;
+        }
+    }
+    if (!group) {
+        tk_error_set_detail("source rows of %u bytes do not fit the shared-memory ring", slot);
+        return TK_ERROR_NOT_IMPLEMENTED;
     }
     k.s_log2 = s_log2;
     k.group_rows = group;

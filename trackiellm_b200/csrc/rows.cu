@@ -15,7 +15,7 @@
 //     in the reference loop, yet 32 rows advance in lock-step.  The normalised
 //     tile is written back flat and coalesced.
 //   * larger rows: a warp per row; exponentials land in a per-warp shared buffer
-//     and are summed in index order (cols <= 4096), or by a shuffle tree beyond.
+//     and are summed in index order (in 4096-element chunks for longer rows).
 //   * exp is tk_dm_expf (bit-identical to the oracle's deterministic mode and
 //     within 2 ulp of libm, inside the reference test's 1e-6 absolute bound).
 #include "tk_common.cuh"
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kRowThreads) softmax_row_kernel(const RowK k) 
     extern __shared__ __align__(16) float rsm[];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool seq = k.cols <= kSeqMaxCols;
-    float* ebuf = rsm + (size_t)warp * (seq ? k.cols : 0);
+    float* ebuf = rsm + (size_t)warp * (seq ? k.cols : kSeqMaxCols);
     for (uint32_t r = blockIdx.x * kRowWarps + warp; r < k.rows; r += gridDim.x * kRowWarps) {
         const float* row = k.in + (size_t)r * k.cols;
         // sequential-scan semantics: mx = x[0]; if (x[j] > mx) ...  (NaN at 0 sticks, NaN elsewhere ignored)
@@ -119,9 +119,17 @@ __global__ void __launch_bounds__(kRowThreads) softmax_row_kernel(const RowK k) 
             for (uint32_t j = lane; j < k.cols; j += 32) __stcs(k.out + (size_t)r * k.cols + j, __fdiv_rn(ebuf[j], sum));
             __syncwarp();
         } else {
-            for (uint32_t j = lane; j < k.cols; j += 32) sum = __fadd_rn(sum, tk_dm_expf(__fsub_rn(__ldg(row + j), mv)));
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) sum = __fadd_rn(sum, __shfl_xor_sync(0xffffffffu, sum, d));
+            // Long rows: the exponentials pass through the per-warp buffer in chunks so the
+            // sum still runs strictly in index order (one running fp32 accumulator, as
+            // tests/tk_gpu_softmax_test.cpp:41-44); the output pass recomputes them.
+            for (uint32_t c0 = 0; c0 < k.cols; c0 += kSeqMaxCols) {
+                const uint32_t n = min(kSeqMaxCols, k.cols - c0);
+                for (uint32_t j = lane; j < n; j += 32) ebuf[j] = tk_dm_expf(__fsub_rn(__ldg(row + c0 + j), mv));
+                __syncwarp();
+                if (lane == 0) for (uint32_t j = 0; j < n; ++j) sum = __fadd_rn(sum, ebuf[j]);
+                __syncwarp();
+            }
+            sum = __shfl_sync(0xffffffffu, sum, 0);
             for (uint32_t j = lane; j < k.cols; j += 32)
                 __stcs(k.out + (size_t)r * k.cols + j, __fdiv_rn(tk_dm_expf(__fsub_rn(__ldg(row + j), mv)), sum));
         }
@@ -145,7 +153,7 @@ static tk_error_code_t launch_rows(const float* in, float* out, uint32_t* amax, 
         softmax_tile_kernel<<<grid, kRowThreads, smem, stream>>>(k);
         return launch_status("softmax_tile_kernel");
     }
-    const size_t smem = cols <= kSeqMaxCols ? (size_t)kRowWarps * cols * 4 : 0;
+    const size_t smem = (size_t)kRowWarps * (cols <= kSeqMaxCols ? cols : kSeqMaxCols) * 4;
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(softmax_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     uint32_t grid = (rows + kRowWarps - 1) / kRowWarps;

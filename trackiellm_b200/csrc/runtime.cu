@@ -4,9 +4,14 @@
 
 #include <stdarg.h>
 #include <string.h>
+#include <atomic>
 #include <mutex>
 
 namespace tkb {
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 static DeviceInfo g_info[64];
 static int g_info_state[64];   // 0 unknown, 1 ok, -1 bad
@@ -89,6 +94,8 @@ extern "C" const char* tk_error_to_string(tk_error_code_t code) {
 }
 
 extern "C" const char* tk_b200_version(void) { return "tk-b200-vision 0.1 (sm_100a)"; }
+
+extern "C" unsigned long long tk_b200_launch_count(void) { return tkb::launch_count(); }
 
 extern "C" int tk_b200_device_count(void) {
     int n = 0;

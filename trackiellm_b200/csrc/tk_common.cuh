@@ -29,6 +29,10 @@ struct DeviceInfo {
 // Cached per-device properties; returns nullptr when no usable CUDA device.
 const DeviceInfo* device_info(int* out_device = nullptr);
 
+// Number of kernels this library has enqueued (every launcher goes through
+// launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
+void count_launch();
+
 // Post-launch check shared by every launcher (reference convention:
 // cudaGetLastError after enqueue, src/gpu/cuda/tk_cuda_kernels.cu:297-300).
 inline tk_error_code_t launch_status(const char* what) {
@@ -37,6 +41,7 @@ inline tk_error_code_t launch_status(const char* what) {
         tk_error_set_detail("%s launch failed: %s", what, cudaGetErrorString(e));
         return TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE;
     }
+    count_launch();
     return TK_SUCCESS;
 }
 

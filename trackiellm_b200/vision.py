@@ -126,7 +126,7 @@ def decode_detections(logits: torch.Tensor, conf_thr: float, *, act: int = ACT_R
 
 def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float, max_detections: int, *,
                   class_agnostic: bool = False, detections: torch.Tensor | None = None,
-                  num_detections: torch.Tensor | None = None):
+                  num_detections: torch.Tensor | None = None, restore: tuple[int, int, int, int] | None = None):
     """tk_kernels_nms_classwise -> (detections int32 [N,max_detections,7], num_detections int32 [N])."""
     _require_cuda(candidates, "candidates")
     n, cap = candidates.shape[0], candidates.shape[1]
@@ -135,7 +135,8 @@ def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float
     if num_detections is None:
         num_detections = torch.empty((n,), dtype=torch.int32, device=candidates.device)
     prm = capi.NmsParams(candidates.data_ptr(), counts.data_ptr(), n, cap, iou_thr, max_detections,
-                         int(class_agnostic), detections.data_ptr(), num_detections.data_ptr())
+                         int(class_agnostic), detections.data_ptr(), num_detections.data_ptr(),
+                         *(restore or (0, 0, 0, 0)))   # restore = (src_w, src_h, in_w, in_h)
     with torch.cuda.device(candidates.device):
         capi.check(capi.lib().tk_kernels_nms_classwise(C.byref(prm), _stream()), "tk_kernels_nms_classwise")
     return detections, num_detections
@@ -307,3 +308,128 @@ class CudaDispatcher:
                                                  C.c_uint32(max_detections), C.c_float(iou_thr), C.c_float(score_thr)),
                    "tk_cuda_tensor_nms")
         return int(n.value)
+
+
+# --------------------------------------------------------------------------- #
+# Batched pipeline (pre-process + decode + class-wise NMS)                      #
+# --------------------------------------------------------------------------- #
+class Pipeline:
+    """tk_b200_pipeline_* — the batched form of what tk_object_detector_detect does per frame
+    (src/vision/tk_object_detector.c:182-203), minus the detector network itself."""
+
+    def __init__(self, *, device_id: int = 0, max_batch: int = 64, chunk_frames: int = 0,
+                 width: int = 1920, height: int = 1080, stride: int = 0, fmt: int = PIXEL_RGB8,
+                 tensor_w: int = 640, tensor_h: int = 640, out_dtype: torch.dtype = torch.float16,
+                 resize: int = RESIZE_STRETCH, arith: int | None = None, pad_value: float = 114.0,
+                 mean=IMAGENET_MEAN, std=IMAGENET_STD, num_proposals: int = 25200, num_classes: int = 80,
+                 act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
+                 max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False):
+        f16 = out_dtype == torch.float16
+        if arith is None:
+            arith = ARITH_FAST if f16 else ARITH_EXACT
+        self.cfg = capi.PipelineConfig(
+            device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, input_width=width,
+            input_height=height, input_stride_bytes=stride, input_format=fmt, tensor_width=tensor_w,
+            tensor_height=tensor_h, tensor_type=OUT_F16 if f16 else OUT_F32, resize_mode=resize, arith=arith,
+            pad_value=pad_value, mean=_f3(mean), std_dev=_f3(std), num_proposals=num_proposals,
+            num_classes=num_classes, activation=act, confidence_threshold=conf_thr, iou_threshold=iou_thr,
+            max_candidates=max_candidates, max_detections=max_detections, class_agnostic=int(class_agnostic),
+            restore_coordinates=int(restore_coordinates))
+        self.out_dtype = out_dtype
+        self.device = torch.device("cuda", device_id)
+        self._h = C.c_void_p()
+        capi.check(capi.lib().tk_b200_pipeline_create(C.byref(self._h), C.byref(self.cfg)), "tk_b200_pipeline_create")
+        L = capi.lib()
+        L.tk_b200_pipeline_frame_bytes.restype = C.c_size_t
+        L.tk_b200_pipeline_frame_bytes.argtypes = [C.c_void_p]
+        L.tk_b200_pipeline_tensor_bytes.restype = C.c_size_t
+        L.tk_b200_pipeline_tensor_bytes.argtypes = [C.c_void_p]
+        self.frame_bytes = int(L.tk_b200_pipeline_frame_bytes(self._h))
+        self.tensor_bytes = int(L.tk_b200_pipeline_tensor_bytes(self._h))
+        self.max_detections = max_detections or 500
+
+    def close(self) -> None:
+        if self._h:
+            capi.lib().tk_b200_pipeline_destroy(C.byref(self._h))
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def update_thresholds(self, conf_thr: float, iou_thr: float) -> None:
+        capi.check(capi.lib().tk_b200_pipeline_update_thresholds(self._h, C.c_float(conf_thr), C.c_float(iou_thr)),
+                   "tk_b200_pipeline_update_thresholds")
+
+    def stage_timing(self, max_calls: int) -> None:
+        capi.check(capi.lib().tk_b200_pipeline_stage_timing(self._h, C.c_uint32(max_calls)), "tk_b200_pipeline_stage_timing")
+
+    def stage_times(self) -> tuple[list[float], int]:
+        """([pre ms, decode ms, nms ms] summed over the recorded calls, number of calls)."""
+        ms = (C.c_double * 3)()
+        n = C.c_uint32(0)
+        capi.check(capi.lib().tk_b200_pipeline_stage_times(self._h, ms, C.byref(n)), "tk_b200_pipeline_stage_times")
+        return [ms[0], ms[1], ms[2]], int(n.value)
+
+    def alloc_outputs(self, n: int, pinned: bool = False):
+        """(tensor, detections int32 [n,max_det,7], counts int32 [n]) on the device, or pinned host (no tensor)."""
+        if pinned:
+            return (None, torch.empty((n, self.max_detections, CAND_WORDS), dtype=torch.int32).pin_memory(),
+                    torch.empty((n,), dtype=torch.int32).pin_memory())
+        return (torch.empty((n, 3, self.cfg.tensor_height, self.cfg.tensor_width), dtype=self.out_dtype, device=self.device),
+                torch.empty((n, self.max_detections, CAND_WORDS), dtype=torch.int32, device=self.device),
+                torch.empty((n,), dtype=torch.int32, device=self.device))
+
+    def process_device(self, frames: torch.Tensor | None, logits: torch.Tensor | None, tensor: torch.Tensor | None,
+                       dets: torch.Tensor | None, counts: torch.Tensor | None) -> None:
+        """tk_b200_pipeline_process_device on torch's current stream (asynchronous, 3 launches)."""
+        n = frames.shape[0] if frames is not None else logits.shape[0]
+        for t, name in ((frames, "frames"), (logits, "logits"), (tensor, "tensor"), (dets, "dets"), (counts, "counts")):
+            if t is not None:
+                _require_cuda(t, name)
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None   # noqa: E731
+        with torch.cuda.device(self.device):
+            capi.check(capi.lib().tk_b200_pipeline_process_device(self._h, ptr(frames), ptr(logits), C.c_uint32(n),
+                                                                  ptr(tensor), ptr(dets), ptr(counts), _stream()),
+                       "tk_b200_pipeline_process_device")
+
+    def process_host(self, frames, logits, dets, counts, tensor=None, logits_on_device: bool = False) -> None:
+        """tk_b200_pipeline_process_host[_frames]: HOST (ideally pinned) torch/numpy buffers in and out; blocks."""
+        def hp(t):
+            if t is None:
+                return None
+            return C.c_void_p(t.data_ptr() if isinstance(t, torch.Tensor) else t.ctypes.data)
+        n = frames.shape[0] if frames is not None else logits.shape[0]
+        fn = capi.lib().tk_b200_pipeline_process_host_frames if logits_on_device else capi.lib().tk_b200_pipeline_process_host
+        capi.check(fn(self._h, hp(frames), hp(logits), C.c_uint32(n), hp(tensor), hp(dets), hp(counts)),
+                   "tk_b200_pipeline_process_host")
+
+
+def postprocess_detections(logits: np.ndarray, *, act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5,
+                           max_detections: int = 500, class_labels: list[str] | None = None,
+                           frame_wh=(0, 0), input_wh=(0, 0)):
+    """tk_b200_postprocess_detections: HOST logits [P,5+C] -> list of (class_id, label, confidence, (x,y,w,h)),
+    the reference's tk_detection_result_t records (src/vision/tk_object_detector.h:66-71)."""
+    logits = np.ascontiguousarray(logits, dtype=np.float32)
+    p, l = logits.shape
+    labels = None
+    nlab = 0
+    if class_labels:
+        nlab = len(class_labels)
+        labels = (C.c_char_p * nlab)(*[s.encode() for s in class_labels])
+    res = C.POINTER(capi.DetectionResult)()
+    cnt = C.c_size_t(0)
+    capi.check(capi.lib().tk_b200_postprocess_detections(
+        logits.ctypes.data_as(C.c_void_p), C.c_uint32(p), C.c_uint32(l - 5), C.c_int(act), C.c_float(conf_thr),
+        C.c_float(iou_thr), C.c_uint32(max_detections), labels, C.c_size_t(nlab), C.c_uint32(frame_wh[0]),
+        C.c_uint32(frame_wh[1]), C.c_uint32(input_wh[0]), C.c_uint32(input_wh[1]), C.byref(res), C.byref(cnt)),
+        "tk_b200_postprocess_detections")
+    out = []
+    for i in range(cnt.value):
+        r = res[i]
+        out.append((int(r.class_id), r.label.decode() if r.label else None, float(r.confidence),
+                    (r.bbox.x, r.bbox.y, r.bbox.w, r.bbox.h)))
+    if cnt.value:
+        capi.lib().tk_object_detector_free_results(C.byref(res))
+    return out
