@@ -285,7 +285,8 @@ def run_b200(args) -> None:
 
     pipe = V.Pipeline(device_id=local, max_batch=B, chunk_frames=args.chunk, width=SRC_W, height=SRC_H,
                       tensor_w=DST, tensor_h=DST, out_dtype=torch.float16, num_proposals=P, num_classes=NC,
-                      act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR, max_detections=MAX_DET)
+                      act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR, max_detections=MAX_DET,
+                      stage_host_logits=args.stage_logits)
     d_tensor, d_dets, d_counts = pipe.alloc_outputs(B)
     _, h_dets, h_counts = pipe.alloc_outputs(B, pinned=True)
     lib = capi.lib()
@@ -374,10 +375,14 @@ def run_b200(args) -> None:
                 "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
                                   "unit": "GB/s", "frac": step_ach / peak},
                 "e2e": {"value": world * B * Ke / e2e_s, "unit": "frames/s",
-                        "h2d_bytes_per_step": B * (FRAME_BYTES + LOGIT_BYTES),
+                        "h2d_bytes_per_step": B * (FRAME_BYTES + (LOGIT_BYTES if args.stage_logits else 0)),
+                        "host_bytes_read_in_place_per_step": 0 if args.stage_logits else B * LOGIT_BYTES,
                         "d2h_bytes_per_step": B * (MAX_DET * 28 + 4), "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke,
                         "api": "tk_b200_pipeline_process_host (pinned host frames + logits in, host detections + counts out; "
-                               "the fp16 tensors stay on the device for the detector)"},
+                               "the fp16 tensors stay on the device for the detector); frames are copied H2D in chunks, "
+                               + ("logits are copied H2D in chunks" if args.stage_logits else
+                                  "the pinned logits are read in place over PCIe by decode_kernel (objectness word of every "
+                                  "row + surviving rows), not copied")},
                 "e2e_device_logits": {"value": world * B * Ke / e2e_dl_s, "unit": "frames/s",
                                       "h2d_bytes_per_step": B * FRAME_BYTES, "d2h_bytes_per_step": B * (MAX_DET * 28 + 4),
                                       "api": "tk_b200_pipeline_process_host_frames (logits already in HBM)"},
@@ -402,6 +407,7 @@ def main() -> None:
     ap.add_argument("--chunk", type=int, default=8, help="frames per in-flight chunk of the host-buffer call")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stage-logits", action="store_true", help="e2e: copy the logits to HBM instead of decoding them in place")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

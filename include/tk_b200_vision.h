@@ -231,6 +231,9 @@ typedef struct {
     uint32_t              max_detections;     /* post-NMS cap per frame; 0 = 500 (tk_object_detector.c:39) */
     int                   class_agnostic;
     int                   restore_coordinates; /* 1 = boxes returned in source-frame px          */
+    int                   stage_host_logits;  /* process_host: 0 = decode reads page-locked host logits in place
+                                                 over PCIe (pageable logits are always staged); 1 = always copy
+                                                 the tensor to HBM first                                         */
 } tk_b200_pipeline_config_t;
 
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out_pipeline, const tk_b200_pipeline_config_t* config);
@@ -248,8 +251,10 @@ TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_device(
 /* HOST inputs and outputs (pinned memory from tk_b200_host_alloc copies by DMA;
  * pageable memory works, slower).  The batch is cut into chunks; upload of chunk
  * k+1, compute of chunk k and download of chunk k-1 overlap on three streams
- * ordered by events.  h_logits may be NULL (pre-process only) and h_frames may
- * be NULL (post-process only).  The model-input tensors stay on the device for
+ * ordered by events.  Page-locked h_logits are not copied at all: decode reads
+ * the objectness word of each row and the surviving rows in place over PCIe
+ * (a tenth of the tensor), concurrently with the frame uploads.  h_logits may
+ * be NULL (pre-process only) and h_frames may be NULL (post-process only).  The model-input tensors stay on the device for
  * the detector (tk_b200_pipeline_tensor_device_ptr) and are also downloaded when
  * h_tensor != NULL.  Blocks until the outputs are in host memory. */
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_host(
@@ -298,7 +303,10 @@ void tk_b200_host_free(void* ptr);
 
 /* Library self-description (no GPU needed). */
 const char* tk_b200_version(void);
-unsigned long long tk_b200_launch_count(void);   /* kernels enqueued by this library so far */
+unsigned long long tk_b200_launch_count(void);
+/* L2 fetch-granularity hint (cudaLimitMaxL2FetchGranularity) of the current device's
+ * context: bytes = 32 / 64 / 128 sets it, 0 only queries; returns the value in effect. */
+int tk_b200_l2_fetch_granularity(int bytes);   /* kernels enqueued by this library so far */
 int tk_b200_device_count(void);
 
 #ifdef __cplusplus

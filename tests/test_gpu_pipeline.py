@@ -56,10 +56,11 @@ def test_process_device_vs_oracle():
         check_dets(d, c, logits)
 
 
+@pytest.mark.parametrize("stage", [False, True])     # logits read in place over PCIe / staged through HBM
 @pytest.mark.parametrize("n,chunk", [(1, 1), (7, 3), (8, 8), (10, 4), (5, 16)])
-def test_process_host_matches_oracle_and_device(n, chunk):
+def test_process_host_matches_oracle_and_device(n, chunk, stage):
     frames, logits = inputs(n, seed0=10)
-    with make_pipe(n, chunk_frames=chunk, out_dtype=torch.float16) as pipe:
+    with make_pipe(n, chunk_frames=chunk, out_dtype=torch.float16, stage_host_logits=stage) as pipe:
         _, hd, hc = pipe.alloc_outputs(n, pinned=True)
         ht = torch.empty((n, 3, 48, 64), dtype=torch.float16).pin_memory()
         hf = torch.from_numpy(frames).pin_memory()

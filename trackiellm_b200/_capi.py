@@ -95,7 +95,7 @@ class PipelineConfig(C.Structure):         # tk_b200_pipeline_config_t
                 ("mean", TkFloat3), ("std_dev", TkFloat3), ("num_proposals", C.c_uint32), ("num_classes", C.c_uint32),
                 ("activation", C.c_int), ("confidence_threshold", C.c_float), ("iou_threshold", C.c_float),
                 ("max_candidates", C.c_uint32), ("max_detections", C.c_uint32), ("class_agnostic", C.c_int),
-                ("restore_coordinates", C.c_int)]
+                ("restore_coordinates", C.c_int), ("stage_host_logits", C.c_int)]
 
 
 class ArgmaxParams(C.Structure):           # tk_b200_argmax_params_t

@@ -12,15 +12,20 @@
 //   (strict; predicate of src/gpu/metal/tk_metal_kernels.metal:868-875 made sequential);
 //   output = kept boxes in sorted order, truncated to max_detections.
 //
-// B200 design (latency-bound, filled by frame-level parallelism):
+// B200 design (latency-bound, filled by frame-level parallelism; shared memory only):
 //   * candidates -> 64-bit keys (~order_key(conf) << 32 | index) + position payload,
-//     bitonic sort in shared memory;
-//   * sorted boxes/classes staged in shared memory;
-//   * the suppression matrix is evaluated in 64-column blocks: each thread builds
-//     one 64-bit row of the diagonal block (bitmask matrix), one thread resolves
-//     the block with a register-carried kept-mask, then all threads sweep the
-//     remaining candidates against the block's kept boxes;
-//   * kept flags -> ballot/prefix compaction in sorted order.
+//     bitonic sort in shared memory; boxes/classes staged in score order;
+//   * a second bitonic sort on (class << 32 | score rank) makes every class one
+//     contiguous segment with score order inside.  Suppression never crosses classes,
+//     so each candidate builds ONE 64-bit mask of the same-class predecessors that
+//     would suppress it (bitmask matrix, block-diagonal by class; neighbouring lanes
+//     run equally long loops, no divergence), and the head of every segment resolves
+//     its segment with a register-carried kept mask — all classes in parallel;
+//   * kept bits are scattered back to score rank and compacted by ballot + prefix;
+//   * a class segment longer than 64 (a crowd of one class, class-agnostic mode)
+//     switches the frame to the blocked path: 64-column blocks of the suppression
+//     matrix over the score-sorted list (diagonal block per thread, one-thread
+//     resolve, CTA-wide sweep).
 #include "tk_common.cuh"
 
 namespace tkb {
@@ -55,36 +60,12 @@ __device__ __forceinline__ float iou_rect(int4 a, int4 b) {
     return uni > 0.0f ? __fdiv_rn(inter, uni) : 0.0f;
 }
 
-__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
-    extern __shared__ __align__(16) uint8_t dsm[];
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(dsm);          // [Kp]
-    int4* box = reinterpret_cast<int4*>(keys + k.Kp);                               // [Kp]
-    uint32_t* pos = reinterpret_cast<uint32_t*>(box + k.Kp);                        // [Kp] position in the input list
-    uint32_t* cls = pos + k.Kp;                                                     // [Kp]
-    uint8_t* dead = reinterpret_cast<uint8_t*>(cls + k.Kp);                         // [Kp]
-    __shared__ unsigned long long diag[64];
-    __shared__ unsigned long long blk_kept;
-    __shared__ uint32_t warp_tot[kNmsWarps];
+// Shared memory: keys u64, box int4, pos u32, cls u32, dead u8, keys2 u64, segmask u64 per entry.
+__host__ __device__ inline size_t nms_smem_bytes(uint32_t Kp) { return (size_t)Kp * (8 + 16 + 4 + 4 + 1 + 8 + 8); }
 
-    const uint32_t frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const tk_b200_candidate_t* in = k.cands + (size_t)frame * k.cap;
-    tk_b200_candidate_t* out = k.dets + (size_t)frame * k.max_det;
-    const uint32_t K = min(k.counts[frame], k.cap);
-    if (K == 0 || k.max_det == 0) { if (tid == 0) k.num_dets[frame] = 0; return; }
-    uint32_t Kp = 64;
-    while (Kp < K) Kp <<= 1;                                       // sort only what this frame needs
-
-    // ---- keys ---------------------------------------------------------------
-    for (uint32_t i = tid; i < Kp; i += kNmsThreads) {
-        unsigned long long key = ~0ull;
-        if (i < K) {
-            uint32_t ck = tk_dm_float_order_key(in[i].confidence);
-            key = ((unsigned long long)(~ck) << 32) | (uint32_t)in[i].index;
-        }
-        keys[i] = key; pos[i] = i;
-    }
-    __syncthreads();
-    // ---- bitonic sort (ascending key == confidence desc, index asc) ----------
+// Bitonic sort of Kp 64-bit keys in shared memory (ascending), optional u32 payload.
+template <bool PAYLOAD>
+__device__ __forceinline__ void bitonic_sort(unsigned long long* keys, uint32_t* pay, uint32_t Kp, uint32_t tid) {
     for (uint32_t kk = 2; kk <= Kp; kk <<= 1) {
         for (uint32_t j = kk >> 1; j > 0; j >>= 1) {
             for (uint32_t t = tid; t < (Kp >> 1); t += kNmsThreads) {
@@ -94,24 +75,151 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
                 bool up = (i & kk) == 0;
                 if ((a > b) == up) {
                     keys[i] = b; keys[l] = a;
-                    uint32_t pa = pos[i]; pos[i] = pos[l]; pos[l] = pa;
+                    if (PAYLOAD) { uint32_t pa = pay[i]; pay[i] = pay[l]; pay[l] = pa; }
                 }
             }
             __syncthreads();
         }
     }
-    // Equal keys (same confidence and same index) can only be distinct input
-    // positions holding identical proposals; any order among them gives the same output.
-    // ---- stage sorted boxes -------------------------------------------------
-    for (uint32_t i = tid; i < K; i += kNmsThreads) {
-        const tk_b200_candidate_t& c = in[pos[i]];
-        box[i] = make_int4(c.bbox.x, c.bbox.y, c.bbox.w, c.bbox.h);
-        cls[i] = k.agnostic ? 0u : c.class_id;
-        dead[i] = 0;
+}
+
+__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
+    extern __shared__ __align__(16) uint8_t dsm[];
+    __shared__ unsigned long long diag[64];
+    __shared__ unsigned long long blk_kept;
+    __shared__ unsigned long long keptbits[kNmsMaxK / 64];
+    __shared__ uint32_t warp_tot[kNmsWarps];
+    __shared__ uint32_t seg_overflow;
+
+    const uint32_t frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const tk_b200_candidate_t* in = k.cands + (size_t)frame * k.cap;
+    tk_b200_candidate_t* out = k.dets + (size_t)frame * k.max_det;
+    const uint32_t K = min(k.counts[frame], k.cap);
+    if (K == 0 || k.max_det == 0) { if (tid == 0) k.num_dets[frame] = 0; return; }
+    uint32_t Kp = 64;
+    while (Kp < K) Kp <<= 1;                                       // sort only what this frame needs
+
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(dsm);          // [Kp] score keys
+    int4* box = reinterpret_cast<int4*>(keys + k.Kp);                               // [Kp] score order
+    uint32_t* pos = reinterpret_cast<uint32_t*>(box + k.Kp);                        // [Kp] position in the input list
+    uint32_t* cls = pos + k.Kp;                                                     // [Kp] score order
+    uint8_t* dead = reinterpret_cast<uint8_t*>(cls + k.Kp);                         // [Kp] blocked path
+    unsigned long long* keys2 = reinterpret_cast<unsigned long long*>(dead + k.Kp); // [Kp] (class << 32 | score rank)
+    unsigned long long* segmask = keys2 + k.Kp;                                     // [Kp] class order
+
+    // ---- score keys -----------------------------------------------------------
+    for (uint32_t i = tid; i < Kp; i += kNmsThreads) {
+        unsigned long long key = ~0ull;
+        if (i < K) {
+            uint32_t ck = tk_dm_float_order_key(in[i].confidence);
+            key = ((unsigned long long)(~ck) << 32) | (uint32_t)in[i].index;
+        }
+        keys[i] = key; pos[i] = i;
+    }
+    if (tid < kNmsMaxK / 64) keptbits[tid] = 0ull;
+    if (tid == 0) seg_overflow = 0;
+    __syncthreads();
+    // ascending key == confidence desc, index asc.  Equal keys (same confidence and
+    // same index) can only be distinct input positions holding identical proposals;
+    // any order among them gives the same output.
+    bitonic_sort<true>(keys, pos, Kp, tid);
+
+    // ---- stage in score order; class keys -----------------------------------------
+    for (uint32_t i = tid; i < Kp; i += kNmsThreads) {
+        unsigned long long k2 = ~0ull;
+        if (i < K) {
+            const tk_b200_candidate_t& c = in[pos[i]];
+            box[i] = make_int4(c.bbox.x, c.bbox.y, c.bbox.w, c.bbox.h);
+            const uint32_t cc = k.agnostic ? 0u : c.class_id;
+            cls[i] = cc; dead[i] = 0;
+            k2 = ((unsigned long long)cc << 32) | i;
+        }
+        keys2[i] = k2;
+    }
+    __syncthreads();
+    // Second sort groups each class into one contiguous segment, score order inside
+    // (a class id of 0xffffffff sorts with the padding but keeps a rank < K, so it is
+    // told apart below by t < K).
+    bitonic_sort<false>(keys2, nullptr, Kp, tid);
+
+    // ---- A. per-candidate suppressor mask inside its class segment -----------------
+    // Suppression never crosses classes.  For the candidate at class-order position t
+    // with R same-class predecessors, bit r of segmask[t] <=> the predecessor of
+    // segment rank r has IoU > thr with it.  Segments longer than 64 (crowds of one
+    // class, class-agnostic mode) take the blocked path below instead.
+    for (uint32_t t = tid; t < K; t += kNmsThreads) {
+        const unsigned long long kt = keys2[t];
+        const uint32_t c = (uint32_t)(kt >> 32);
+        const int4 me = box[(uint32_t)kt];
+        unsigned long long mdist = 0;                              // bit d-1: predecessor at distance d
+        uint32_t R = 0;
+        for (uint32_t j = t; j-- > 0;) {
+            const unsigned long long kj = keys2[j];
+            if ((uint32_t)(kj >> 32) != c) break;
+            if (R == 63) { seg_overflow = 1; break; }           // a segment longer than 64
+            if (iou_rect(box[(uint32_t)kj], me) > k.thr) mdist |= 1ull << R;
+            ++R;
+        }
+        // distance d = 1..R maps to segment rank R - d
+        segmask[t] = R ? (__brevll(mdist) >> (64 - R)) : 0ull;
+        dead[t] = (uint8_t)(R == 0);                               // (fast path only) 1 = head of a segment
     }
     __syncthreads();
 
-    // ---- blocked greedy suppression -----------------------------------------
+    uint32_t run = 0;
+    if (!seg_overflow) {
+        // ---- B. each segment head resolves its segment sequentially (<= 64 steps) ----
+        for (uint32_t t = tid; t < K; t += kNmsThreads) {
+            if (!dead[t]) continue;
+            const uint32_t c = (uint32_t)(keys2[t] >> 32);
+            unsigned long long kept = 0;
+            for (uint32_t r = 0; t + r < K; ++r) {
+                const unsigned long long kr = keys2[t + r];
+                if ((uint32_t)(kr >> 32) != c) break;
+                if ((segmask[t + r] & kept) == 0) {
+                    kept |= 1ull << r;
+                    const uint32_t i = (uint32_t)kr;                // score rank
+                    atomicOr(&keptbits[i >> 6], 1ull << (i & 63));
+                }
+            }
+        }
+        __syncthreads();
+        // ---- C. kept bitmap -> ordered compaction in score order ---------------------
+        for (uint32_t base = 0; base < K; base += kNmsThreads) {
+            const uint32_t i = base + tid;
+            const bool keep = i < K && ((keptbits[i >> 6] >> (i & 63)) & 1ull);
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            if (lane == 0) warp_tot[warp] = __popc(bal);
+            __syncthreads();
+            uint32_t before = 0, tot = 0;
+#pragma unroll
+            for (int w = 0; w < kNmsWarps; ++w) { uint32_t t = warp_tot[w]; before += (uint32_t)w < warp ? t : 0u; tot += t; }
+            const uint32_t o = run + before + __popc(bal & ((1u << lane) - 1u));
+            if (keep && o < k.max_det) {
+                tk_b200_candidate_t c = in[pos[i]];
+                if (k.restore) {
+                    c.bbox.x = __float2int_rz(__fmul_rn((float)c.bbox.x, k.sx));
+                    c.bbox.y = __float2int_rz(__fmul_rn((float)c.bbox.y, k.sy));
+                    c.bbox.w = __float2int_rz(__fmul_rn((float)c.bbox.w, k.sx));
+                    c.bbox.h = __float2int_rz(__fmul_rn((float)c.bbox.h, k.sy));
+                }
+                out[o] = c;
+            }
+            run += tot;
+            __syncthreads();
+            if (run >= k.max_det) break;
+        }
+        if (tid == 0) k.num_dets[frame] = min(run, k.max_det);
+        return;
+    }
+
+    // =========================================================================
+    // Blocked path (a class segment longer than 64): 64-column blocks of the
+    // suppression matrix over the score-sorted list.
+    // =========================================================================
+    for (uint32_t i = tid; i < K; i += kNmsThreads) dead[i] = 0;   // box/cls are staged in score order already
+    __syncthreads();
+
     for (uint32_t b0 = 0; b0 < K; b0 += 64) {
         const uint32_t bn = min(64u, K - b0);
         // (a) diagonal block of the bitmask matrix: bit j of diag[i] <=> j < i suppresses i
@@ -155,7 +263,6 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
     }
 
     // ---- ordered compaction of the survivors --------------------------------
-    uint32_t run = 0;
     for (uint32_t base = 0; base < K; base += kNmsThreads) {
         const uint32_t i = base + tid;
         const bool keep = i < K && !dead[i];
@@ -212,7 +319,7 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
         k.sx = (float)p->restore_src_width / (float)p->restore_in_width;
         k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
     }
-    const size_t smem = (size_t)k.Kp * (8 + 16 + 4 + 4 + 1);
+    const size_t smem = nms_smem_bytes(k.Kp);
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     nms_kernel<<<p->num_frames, kNmsThreads, smem, stream>>>(k);

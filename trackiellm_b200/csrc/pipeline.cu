@@ -37,7 +37,8 @@ struct tk_b200_pipeline_s {
     tk_b200_pipeline_config_t cfg;
     size_t frame_bytes, logit_bytes, tensor_bytes;     // per frame
     uint32_t chunk;
-    cudaStream_t s_up, s_compute, s_down;
+    cudaStream_t s_up, s_compute, s_down, s_post;
+    cudaEvent_t ev_post;
     cudaEvent_t ev_uploaded[tkb::kSlots], ev_computed[tkb::kSlots], ev_downloaded[tkb::kSlots];
     uint8_t* d_frames[tkb::kSlots];                    // [chunk][frame_bytes (+ slack)]
     float*   d_logits[tkb::kSlots];                    // [chunk][P][5+C]
@@ -71,6 +72,7 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->s_up) { cudaStreamSynchronize(p->s_up); }
         if (p->s_compute) { cudaStreamSynchronize(p->s_compute); }
         if (p->s_down) { cudaStreamSynchronize(p->s_down); }
+        if (p->s_post) { cudaStreamSynchronize(p->s_post); }
         for (int i = 0; i < kSlots; ++i) {
             if (p->d_frames[i]) cudaFree(p->d_frames[i]);
             if (p->d_logits[i]) cudaFree(p->d_logits[i]);
@@ -88,6 +90,8 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->s_up) cudaStreamDestroy(p->s_up);
         if (p->s_compute) cudaStreamDestroy(p->s_compute);
         if (p->s_down) cudaStreamDestroy(p->s_down);
+        if (p->s_post) cudaStreamDestroy(p->s_post);
+        if (p->ev_post) cudaEventDestroy(p->ev_post);
         cudaGetLastError();
     }
     delete p;
@@ -124,7 +128,9 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
 
     bool ok = cudaStreamCreateWithFlags(&p->s_up, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&p->s_compute, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithFlags(&p->s_down, cudaStreamNonBlocking) == cudaSuccess;
+              cudaStreamCreateWithFlags(&p->s_down, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_post, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&p->ev_post, cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < kSlots; ++i) {
         ok = cudaEventCreateWithFlags(&p->ev_uploaded[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&p->ev_computed[i], cudaEventDisableTiming) == cudaSuccess &&
@@ -268,13 +274,23 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
 
 #define TK_PIPE_TRY(call) TK_CUDA_TRY(call, TK_ERROR_GPU_MEMORY_COPY_FAILED)
 
-// Chunked three-stream flow.  Slot s = chunk % kSlots owns one frame buffer, one
-// logit buffer and three events:
+// Host-buffer flow.
+//
+// Frames: chunked three-stream flow.  Slot s = chunk % kSlots owns one frame buffer
+// (and one logit buffer) and its events:
 //   upload(k)   waits computed(k - kSlots)   (the slot's previous kernels are done reading)
 //   compute(k)  waits uploaded(k)
 //   download(k) waits computed(k)
 // Outputs (tensor, detections, counts) have per-frame homes for the whole batch,
 // so downloads never block later compute.
+//
+// Logits: decode needs 4 bytes of every 340-byte row (the objectness word) and the
+// full row only for the few hundred survivors, so copying the tensor to HBM first
+// moves ~10x more bytes over PCIe than the kernel reads.  When the caller's logits
+// are in page-locked host memory (tk_b200_host_alloc / cudaHostAlloc: device-
+// addressable under UVA) decode_kernel reads them IN PLACE over PCIe: one launch
+// for the whole batch on its own stream, concurrent with the frame uploads.
+// Pageable logits (or stage_host_logits = 1) are staged through HBM chunk by chunk.
 static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_frames, const float* h_logits,
                                          const float* d_logits_all, uint32_t n, void* h_tensor,
                                          tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
@@ -288,8 +304,26 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
     DevScope scope(p->cfg.device_id);
     if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
     const size_t det_stride = p->cfg.max_detections;
-    const uint32_t chunks = (n + p->chunk - 1) / p->chunk;
     tk_error_code_t rc = TK_SUCCESS;
+
+    // Whole-batch post-process when the logits are device-addressable where they lie.
+    const float* logits_in_place = d_logits_all;
+    if (h_logits && !p->cfg.stage_host_logits) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, h_logits) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+            logits_in_place = static_cast<const float*>(at.devicePointer);
+        else
+            cudaGetLastError();
+    }
+    if (logits_in_place) {
+        rc = run_kernels(p, nullptr, logits_in_place, n, nullptr, p->d_cands, p->d_counts, p->d_dets, p->d_ndets, p->s_post);
+        if (rc == TK_SUCCESS) {
+            TK_PIPE_TRY(cudaMemcpyAsync(h_dets, p->d_dets, (size_t)n * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_post));
+            TK_PIPE_TRY(cudaMemcpyAsync(h_ndets, p->d_ndets, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post));
+        }
+    }
+    const bool chunk_logits = h_logits && !logits_in_place;
+    const uint32_t chunks = (h_frames || chunk_logits) ? (n + p->chunk - 1) / p->chunk : 0;
     for (uint32_t k = 0; k < chunks && rc == TK_SUCCESS; ++k) {
         const int s = (int)(k % kSlots);
         const uint32_t f0 = k * p->chunk;
@@ -299,23 +333,21 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
         if (h_frames)
             TK_PIPE_TRY(cudaMemcpyAsync(p->d_frames[s], static_cast<const uint8_t*>(h_frames) + (size_t)f0 * p->frame_bytes,
                                         (size_t)m * p->frame_bytes, cudaMemcpyHostToDevice, p->s_up));
-        if (h_logits)
+        if (chunk_logits)
             TK_PIPE_TRY(cudaMemcpyAsync(p->d_logits[s], reinterpret_cast<const uint8_t*>(h_logits) + (size_t)f0 * p->logit_bytes,
                                         (size_t)m * p->logit_bytes, cudaMemcpyHostToDevice, p->s_up));
         TK_PIPE_TRY(cudaEventRecord(p->ev_uploaded[s], p->s_up));
         // ---- compute
         TK_PIPE_TRY(cudaStreamWaitEvent(p->s_compute, p->ev_uploaded[s], 0));
-        const float* dl = h_logits ? p->d_logits[s]
-                                   : (d_logits_all ? reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(d_logits_all) + (size_t)f0 * p->logit_bytes)
-                                                   : nullptr);
-        rc = run_kernels(p, h_frames ? p->d_frames[s] : nullptr, dl, m, p->d_tensor + (size_t)f0 * p->tensor_bytes,
+        rc = run_kernels(p, h_frames ? p->d_frames[s] : nullptr, chunk_logits ? p->d_logits[s] : nullptr, m,
+                         p->d_tensor + (size_t)f0 * p->tensor_bytes,
                          p->d_cands + (size_t)f0 * p->cfg.max_candidates, p->d_counts + f0,
                          p->d_dets + (size_t)f0 * det_stride, p->d_ndets + f0, p->s_compute);
         if (rc != TK_SUCCESS) break;
         TK_PIPE_TRY(cudaEventRecord(p->ev_computed[s], p->s_compute));
         // ---- download
-        TK_PIPE_TRY(cudaStreamWaitEvent(p->s_down, p->ev_computed[s], 0));
-        if (have_logits) {
+        if (chunk_logits || (h_tensor && h_frames)) TK_PIPE_TRY(cudaStreamWaitEvent(p->s_down, p->ev_computed[s], 0));
+        if (chunk_logits) {
             TK_PIPE_TRY(cudaMemcpyAsync(h_dets + (size_t)f0 * det_stride, p->d_dets + (size_t)f0 * det_stride,
                                         (size_t)m * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_down));
             TK_PIPE_TRY(cudaMemcpyAsync(h_ndets + f0, p->d_ndets + f0, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_down));
@@ -326,13 +358,15 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
                                         cudaMemcpyDeviceToHost, p->s_down));
     }
     // Drain even after an error so no copy is left in flight on the caller's buffers.
-    cudaError_t e1 = cudaStreamSynchronize(p->s_up), e2 = cudaStreamSynchronize(p->s_compute), e3 = cudaStreamSynchronize(p->s_down);
-    if (rc == TK_SUCCESS && (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess)) {
-        cudaError_t e = e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3);
-        tk_error_set_detail("pipeline drain: %s", cudaGetErrorString(e));
-        cudaGetLastError();
-        rc = TK_ERROR_CUDA_KERNEL_FAILURE;
+    cudaError_t es[4] = {cudaStreamSynchronize(p->s_up), cudaStreamSynchronize(p->s_compute),
+                         cudaStreamSynchronize(p->s_down), cudaStreamSynchronize(p->s_post)};
+    for (int i = 0; i < 4; ++i) {
+        if (es[i] != cudaSuccess && rc == TK_SUCCESS) {
+            tk_error_set_detail("pipeline drain: %s", cudaGetErrorString(es[i]));
+            rc = TK_ERROR_CUDA_KERNEL_FAILURE;
+        }
     }
+    cudaGetLastError();
     return rc;
 }
 

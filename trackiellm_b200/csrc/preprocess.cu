@@ -235,9 +235,10 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
         const uint8_t* src = base + (size_t)row * p.src_stride;
         if constexpr (TMA) {
             if (tid == 0) {
-                // The slot's previous copy must have landed before its barrier is re-armed
-                // (a row no consumer waited on may still be in flight).
-                if (seq >= S) mbar_wait(&bars[slot], ((seq >> p.s_log2) - 1u) & 1u);
+                // Invariant: every staged row is waited on by a consumer before its slot comes
+                // round again (dense: y_ratio < 2 leaves no unsampled row between y and y+1 of
+                // consecutive output rows; sparse: only sampled rows are staged), so the slot's
+                // previous copy has landed and its barrier may be re-armed without a wait here.
                 if constexpr (FMT == FMT_I420) {
                     uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
                     mbar_arrive_expect_tx(&bars[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);

@@ -95,6 +95,17 @@ extern "C" const char* tk_error_to_string(tk_error_code_t code) {
 
 extern "C" const char* tk_b200_version(void) { return "tk-b200-vision 0.1 (sm_100a)"; }
 
+// L2 fetch granularity hint of the current device's context (bytes: 32, 64 or 128;
+// 0 = query only).  Returns the value in effect, or -1 on error.  Sector-strided
+// scans (decode pass 1 reads 4 bytes of every 340-byte row) move fewer DRAM bytes
+// with a small granularity; streaming kernels are indifferent.
+extern "C" int tk_b200_l2_fetch_granularity(int bytes) {
+    if (bytes > 0 && cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes) != cudaSuccess) { cudaGetLastError(); return -1; }
+    size_t v = 0;
+    if (cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return (int)v;
+}
+
 extern "C" unsigned long long tk_b200_launch_count(void) { return tkb::launch_count(); }
 
 extern "C" int tk_b200_device_count(void) {

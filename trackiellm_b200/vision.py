@@ -323,7 +323,8 @@ class Pipeline:
                  resize: int = RESIZE_STRETCH, arith: int | None = None, pad_value: float = 114.0,
                  mean=IMAGENET_MEAN, std=IMAGENET_STD, num_proposals: int = 25200, num_classes: int = 80,
                  act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
-                 max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False):
+                 max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False,
+                 stage_host_logits: bool = False):
         f16 = out_dtype == torch.float16
         if arith is None:
             arith = ARITH_FAST if f16 else ARITH_EXACT
@@ -334,7 +335,7 @@ class Pipeline:
             pad_value=pad_value, mean=_f3(mean), std_dev=_f3(std), num_proposals=num_proposals,
             num_classes=num_classes, activation=act, confidence_threshold=conf_thr, iou_threshold=iou_thr,
             max_candidates=max_candidates, max_detections=max_detections, class_agnostic=int(class_agnostic),
-            restore_coordinates=int(restore_coordinates))
+            restore_coordinates=int(restore_coordinates), stage_host_logits=int(stage_host_logits))
         self.out_dtype = out_dtype
         self.device = torch.device("cuda", device_id)
         self._h = C.c_void_p()
