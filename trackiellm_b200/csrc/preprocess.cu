@@ -10,9 +10,15 @@
 //     per CTA (grid = resident CTAs), so every source row is fetched once per
 //     CTA and the load is balanced to +-1 row.
 //   * Source rows stream through a shared-memory ring filled by TMA 1-D bulk
-//     copies (cp.async.bulk + mbarrier complete_tx), issued by one thread, many
-//     rows ahead of the consumers; an unaligned source falls back to a
-//     cooperative byte copy into the same ring.
+//     copies (cp.async.bulk + mbarrier complete_tx).  The CTA is warp-specialised:
+//     ONE PRODUCER WARP walks the CTA's source-row sequence and issues the copies
+//     as slots free up; the consumer warps wait on a slot's `full` barrier, read,
+//     and arrive on its `empty` barrier.  No CTA-wide barrier after set-up, so the
+//     warps drift apart and loads, gathers and stores overlap.  An unaligned
+//     source (TMA's 16-byte rules) is copied by the producer warp with aligned
+//     32-bit loads + funnel shift into the same ring.
+//   * y_ratio >= 2 (4K): only the two source rows each output row samples are
+//     staged ("sparse"); rows nothing samples are never fetched.
 //   * Each thread produces 4 consecutive output pixels x 3 channels from the
 //     ring (3 LDS.32 + funnel shift per source row and pixel, bank-conflict-free
 //     at the 1080p->640 ratio) and writes one 128-bit (fp32) or 64-bit (fp16)
@@ -44,7 +50,7 @@ struct PreK {
     uint32_t u_slot_off, v_slot_off;   // I420 offsets inside a ring slot
     uint32_t tab_w;         // dst_w rounded up to 4
     uint32_t ring_off;      // byte offset of the ring in dynamic smem
-    uint32_t group_rows;    // output rows per consumer group
+    uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty output rows in flight
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
 };
@@ -160,25 +166,53 @@ __device__ __forceinline__ void item_src_rows(const PreK& p, uint32_t h0, uint32
     nrows = p.sparse ? (int)(2u * (b - a)) : src_row_of(p, b - 1) + 2 - ylo;
 }
 
+// Copy `nb` bytes from a possibly unaligned global address into 4-byte-aligned shared
+// memory, one warp, aligned 32-bit loads + funnel shift (fallback when TMA's 16-byte
+// rules do not hold).  Never reads a global word that holds no byte of [src, src+nb).
+__device__ __forceinline__ void warp_copy_unaligned(uint8_t* dst, const uint8_t* src, uint32_t nb, uint32_t lane) {
+    const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(src - shift);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst);
+    const uint32_t nd = (nb + 3) >> 2;
+    for (uint32_t i = lane; i < nd; i += 32) {
+        uint32_t lo = __ldg(sw + i);
+        uint32_t hi = (shift && 4u * (i + 1) < shift + nb) ? __ldg(sw + i + 1) : 0u;
+        dw[i] = __funnelshift_r(lo, hi, shift * 8);
+    }
+}
+
+// Block = consumer threads (tx * ty, tx a multiple of 32) + one producer warp.
+//   consumers: warp (cy, *) produces output rows h0+cy, h0+cy+ty, ...; before a row it
+//              publishes `progress[warp]` = the first ring sequence number the row
+//              needs (everything below is released), waits for its two source rows on
+//              their `full` barriers and computes.
+//   producer : walks the CTA's source-row sequence; sequence q may overwrite slot
+//              q mod S once q - S < min(progress[*]); lane 0 then issues the TMA bulk
+//              copy (or the warp copies) that completes full[slot].
+// There is no CTA-wide barrier after set-up.
 template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
-__global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
+__global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                 // 64 x 8 B
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);                 // 32 x 8 B
+    volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(full + 32);   // one per consumer warp (<= 32)
+    volatile uint32_t* staged = progress + 32;   // number of sequence numbers the producer has armed so far
     int* xb_tab = reinterpret_cast<int*>(smem + 512);
     float* xd_tab = reinterpret_cast<float*>(smem + 512 + 4 * p.tab_w);
     uint8_t* ring = smem + p.ring_off;
 
-    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-    const int nthr = blockDim.x * blockDim.y;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t ncons = p.tx * p.ty;
     const uint32_t S = 1u << p.s_log2, smask = S - 1;
 
-    if (TMA && tid == 0) {
-        for (uint32_t s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+    if (tid == 0) {
+        for (uint32_t s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_fence_init();
     }
+    if (tid < 32) progress[tid] = tid < (ncons >> 5) ? 0u : 0xffffffffu;
+    if (tid == 0) *staged = 0u;
     // Column table: byte offset of the left source pixel and x weight
     // (src/vision/tk_image_preprocessor.c:48,50,52).
-    for (uint32_t w = tid; w < p.tab_w; w += nthr) {
+    for (uint32_t w = tid; w < p.tab_w; w += blockDim.x) {
         uint32_t wc = min(w, p.dst_w - 1);
         int xb = -1; float xd = 0.0f;
         if (!LBOX || (wc - p.pad_left) < p.new_w) {
@@ -208,75 +242,69 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
         return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
     };
 
-    // ---- producer cursor (uniform across threads; only tid 0 issues TMA) ----
-    uint32_t pf = f_first, p_seq = 0;
-    int p_row = 0, p_end = -1;           // dense: next source row to stage, last row of the item
-    uint32_t p_h = 0, p_hend = 0, p_k = 0;   // sparse: output row being staged, end row, 0/1 = top/bottom source row
-    bool p_valid = false;
-    const uint8_t* p_base = nullptr;
-    auto producer_seek = [&]() {         // position on the next item that needs source rows
-        while (pf <= f_last) {
-            uint32_t h0, h1, a; item_rows(pf, h0, h1);
+    // ======================= producer warp =======================================
+    if (tid >= ncons) {
+        const uint32_t lane = tid - ncons;
+        uint32_t seq = 0, min_rel = 0;       // every sequence below min_rel has been released by all consumer warps
+        for (uint32_t f = f_first; f <= f_last; ++f) {
+            uint32_t h0, h1, a; item_rows(f, h0, h1);
             int ylo, n; item_src_rows(p, h0, h1, ylo, n, a);
-            if (n > 0) {
-                p_row = ylo; p_end = ylo + n - 1;
-                p_h = a; p_hend = a + (uint32_t)n / 2; p_k = 0;
-                p_base = frame_ptr(pf); p_valid = true; return;
-            }
-            ++pf;
-        }
-        p_valid = false;
-    };
-    producer_seek();
-
-    auto stage_row = [&](uint32_t seq, const uint8_t* base, int row) {
-        const uint32_t slot = seq & smask;
-        uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
-        const uint8_t* src = base + (size_t)row * p.src_stride;
-        if constexpr (TMA) {
-            if (tid == 0) {
-                // Invariant: every staged row is waited on by a consumer before its slot comes
-                // round again (dense: y_ratio < 2 leaves no unsampled row between y and y+1 of
-                // consecutive output rows; sparse: only sampled rows are staged), so the slot's
-                // previous copy has landed and its barrier may be re-armed without a wait here.
-                if constexpr (FMT == FMT_I420) {
-                    uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
-                    mbar_arrive_expect_tx(&bars[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
-                    bulk_g2s(dst, src, p.copy_bytes, &bars[slot]);
-                    bulk_g2s(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &bars[slot]);
-                    bulk_g2s(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &bars[slot]);
+            const uint8_t* base = frame_ptr(f);
+            for (int r = 0; r < n; ++r, ++seq) {
+                const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
+                const uint32_t slot = seq & smask;
+                if (seq >= S) {
+                    while (seq - S >= min_rel) {                   // slot still holds a row somebody may read
+                        min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
+                        if (seq - S >= min_rel) __nanosleep(100);
+                    }
+                    __threadfence_block();
+                    // every staged row is waited on by the warps that sample it before they move
+                    // past it, so the slot's previous copy has landed; the check is free then.
+                    if (TMA && lane == 0) mbar_wait(&full[slot], ((seq >> p.s_log2) - 1u) & 1u);
+                }
+                uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
+                const uint8_t* src = base + (size_t)row * p.src_stride;
+                if constexpr (TMA) {
+                    if (lane == 0) {
+                        fence_proxy_async();
+                        if constexpr (FMT == FMT_I420) {
+                            const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+                            mbar_arrive_expect_tx(&full[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
+                            bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
+                            bulk_g2s(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
+                            bulk_g2s(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
+                        } else {
+                            mbar_arrive_expect_tx(&full[slot], p.copy_bytes);
+                            bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
+                        }
+                    }
                 } else {
-                    mbar_arrive_expect_tx(&bars[slot], p.copy_bytes);
-                    bulk_g2s(dst, src, p.copy_bytes, &bars[slot]);
+                    const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
+                    warp_copy_unaligned(dst, src, nb, lane);
+                    if constexpr (FMT == FMT_I420) {
+                        const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+                        warp_copy_unaligned(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
+                        warp_copy_unaligned(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full[slot]);
                 }
-            }
-        } else {
-            const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
-            for (uint32_t i = tid; i < nb; i += nthr) dst[i] = __ldg(src + i);
-            if constexpr (FMT == FMT_I420) {
-                uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
-                const uint8_t* us = base + p.u_off + (size_t)cr * p.chroma_pitch;
-                const uint8_t* vs = base + p.v_off + (size_t)cr * p.chroma_pitch;
-                for (uint32_t i = tid; i < (p.src_w >> 1); i += nthr) {
-                    dst[p.u_slot_off + i] = __ldg(us + i);
-                    dst[p.v_slot_off + i] = __ldg(vs + i);
-                }
+                // A waiter tells phases apart by parity only, so it may look at full[slot] for
+                // sequence q only once q has been armed (which implies q - S has completed).
+                if (lane == 0) { __threadfence_block(); *staged = seq + 1; }
             }
         }
-    };
-    auto produce = [&](uint32_t limit_seq) {
-        if (TMA && tid == 0) fence_proxy_async();
-        while (p_valid && (int32_t)(p_seq - limit_seq) < 0) {
-            if (p.sparse) {
-                stage_row(p_seq, p_base, src_row_of(p, p_h) + (int)p_k);
-                ++p_seq;
-                if (++p_k == 2) { p_k = 0; if (++p_h >= p_hend) { ++pf; producer_seek(); } }
-            } else {
-                stage_row(p_seq, p_base, p_row);
-                ++p_seq;
-                if (++p_row > p_end) { ++pf; producer_seek(); }
-            }
-        }
+        return;
+    }
+
+    // ======================= consumer warps ======================================
+    const uint32_t cx = tid % p.tx, cy = tid / p.tx, lane = tid & 31;
+    uint32_t rel = 0;                    // next sequence number this warp has not released yet
+    auto pass_to = [&](uint32_t target) {        // release every sequence below `target`
+        __syncwarp();                            // all lanes are done reading the rows being released
+        if (lane == 0) { __threadfence_block(); progress[tid >> 5] = target; }
+        rel = target;
     };
 
     // Pad rows/pixels (letterbox) carry the same normalisation as real pixels.
@@ -291,95 +319,80 @@ __global__ void __launch_bounds__(320, 2) preprocess_kernel(const PreK p) {
     for (uint32_t f = f_first; f <= f_last; ++f) {
         uint32_t h0, h1; item_rows(f, h0, h1);
         int ylo, nrows; uint32_t a_first; item_src_rows(p, h0, h1, ylo, nrows, a_first);
-        for (uint32_t hg = h0; hg < h1; hg += p.group_rows) {
-            const uint32_t hge = min(hg + p.group_rows, h1);
-            // First source row this group still needs -> how far the producer may run.
-            uint32_t need_seq = seq_base;
-            {
-                uint32_t a = max(hg, p.pad_top), b = min(hge, p.pad_top + p.new_h);
-                if (a < b) {
-                    need_seq = seq_base + (p.sparse ? 2u * (a - a_first) : (uint32_t)(src_row_of(p, a) - ylo));
-                } else if (hg >= p.pad_top + p.new_h) {
-                    need_seq = seq_base + (uint32_t)nrows;
-                }
+        for (uint32_t h = h0 + cy; h < h1; h += p.ty) {
+            const bool vin = !LBOX || (h - p.pad_top) < p.new_h;
+            float yd = 0.0f, omy = 1.0f;
+            const uint8_t* row0 = ring;
+            const uint8_t* row1 = ring;
+            if (vin) {
+                float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
+                int y = min(__float2int_rz(gy), (int)p.src_h - 2);
+                yd = __fsub_rn(gy, (float)y);
+                omy = __fsub_rn(1.0f, yd);
+                const uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
+                if (rel != q0) pass_to(q0);
+                row0 = ring + (size_t)(q0 & smask) * p.slot_bytes;
+                row1 = ring + (size_t)(q1 & smask) * p.slot_bytes;
+                while (*staged <= q1) __nanosleep(32);
+                __threadfence_block();
+                mbar_wait_backoff(&full[q0 & smask], (q0 >> p.s_log2) & 1u);
+                mbar_wait_backoff(&full[q1 & smask], (q1 >> p.s_log2) & 1u);
             }
-            produce(need_seq + S);
-            if (!TMA) __syncthreads();
-
-            for (uint32_t h = hg + threadIdx.y; h < hge; h += blockDim.y) {
-                const bool vin = !LBOX || (h - p.pad_top) < p.new_h;
-                float yd = 0.0f, omy = 1.0f;
-                const uint8_t* row0 = ring;
-                const uint8_t* row1 = ring;
+            for (uint32_t q = cx; q < Q; q += p.tx) {
+                float o[3][4];
                 if (vin) {
-                    float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
-                    int y = min(__float2int_rz(gy), (int)p.src_h - 2);
-                    yd = __fsub_rn(gy, (float)y);
-                    omy = __fsub_rn(1.0f, yd);
-                    uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
-                    row0 = ring + (size_t)(q0 & smask) * p.slot_bytes;
-                    row1 = ring + (size_t)(q1 & smask) * p.slot_bytes;
-                    if (TMA) {
-                        mbar_wait(&bars[q0 & smask], (q0 >> p.s_log2) & 1u);
-                        mbar_wait(&bars[q1 & smask], (q1 >> p.s_log2) & 1u);
+                    const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+                    const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
+                    const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
+                    const float xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (LBOX && xbs[j] < 0) {
+                            o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2];
+                        } else {
+                            float m[4][3];
+                            fetch_quad<FMT>(p, row0, row1, xbs[j], m);
+                            const float xd = xds[j], omx = __fsub_rn(1.0f, xd);
+#pragma unroll
+                            for (int c = 0; c < 3; ++c)
+                                o[c][j] = blend_norm<EXACT>(p, c, m[0][c], m[1][c], m[2][c], m[3][c], xd, omx, yd, omy);
+                        }
                     }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
                 }
-                for (uint32_t q = threadIdx.x; q < Q; q += blockDim.x) {
-                    float o[3][4];
-                    if (vin) {
-                        const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
-                        const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
-                        const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
-                        const float xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+                const size_t pix = (size_t)h * p.dst_w + 4u * q;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (LBOX && xbs[j] < 0) {
-                                o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2];
-                            } else {
-                                float m[4][3];
-                                fetch_quad<FMT>(p, row0, row1, xbs[j], m);
-                                const float xd = xds[j], omx = __fsub_rn(1.0f, xd);
-#pragma unroll
-                                for (int c = 0; c < 3; ++c)
-                                    o[c][j] = blend_norm<EXACT>(p, c, m[0][c], m[1][c], m[2][c], m[3][c], xd, omx, yd, omy);
-                            }
+                for (int c = 0; c < 3; ++c) {
+                    const size_t e = ((size_t)f * 3 + c) * plane + pix;
+                    if (p.vec_store) {
+                        if constexpr (F16) {
+                            __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
+                            __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
+                            uint2 v;
+                            v.x = *reinterpret_cast<uint32_t*>(&lo);
+                            v.y = *reinterpret_cast<uint32_t*>(&hi);
+                            __stcs(reinterpret_cast<uint2*>(static_cast<__half*>(p.out) + e), v);
+                        } else {
+                            __stcs(reinterpret_cast<float4*>(static_cast<float*>(p.out) + e),
+                                   make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
                         }
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
-                    }
-                    const size_t pix = (size_t)h * p.dst_w + 4u * q;
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const size_t e = ((size_t)f * 3 + c) * plane + pix;
-                        if (p.vec_store) {
-                            if constexpr (F16) {
-                                __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
-                                __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
-                                uint2 v;
-                                v.x = *reinterpret_cast<uint32_t*>(&lo);
-                                v.y = *reinterpret_cast<uint32_t*>(&hi);
-                                __stcs(reinterpret_cast<uint2*>(static_cast<__half*>(p.out) + e), v);
-                            } else {
-                                __stcs(reinterpret_cast<float4*>(static_cast<float*>(p.out) + e),
-                                       make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                if (4u * q + j < p.dst_w) {
-                                    if constexpr (F16) static_cast<__half*>(p.out)[e + j] = __float2half_rn(o[c][j]);
-                                    else static_cast<float*>(p.out)[e + j] = o[c][j];
-                                }
+                        for (int j = 0; j < 4; ++j) {
+                            if (4u * q + j < p.dst_w) {
+                                if constexpr (F16) static_cast<__half*>(p.out)[e + j] = __float2half_rn(o[c][j]);
+                                else static_cast<float*>(p.out)[e + j] = o[c][j];
                             }
                         }
                     }
                 }
             }
-            __syncthreads();   // every reader is done with rows < next group's first row
         }
         seq_base += (uint32_t)nrows;
     }
+    pass_to(0xffffffffu);                        // done: nothing this warp could still read
 }
 
 // ------------------------------------------------------------------------- //
@@ -523,43 +536,42 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     k.ring_off = (512 + 8 * k.tab_w + 127) & ~127u;
     k.vec_store = (k.dst_w % 4 == 0) && (reinterpret_cast<uintptr_t>(prm->d_output) % 16 == 0);
 
-    // Block shape: threads along x cover the row's pixel quads.
+    // Consumer shape: tx threads along x cover the row's pixel quads, ty rows in flight;
+    // one more warp produces.
     const uint32_t Q = k.tab_w / 4;
     uint32_t tx = Q >= 160 ? 160 : ((Q + 31) & ~31u);
-    if (tx > 320) tx = 320;
     uint32_t ty = 320 / tx; if (ty < 1) ty = 1;
-    dim3 block(tx, ty);
 
-    // Ring depth: largest power of two that fits the budget; two CTAs per SM when possible.
+    // Ring depth: the largest power of two (<= 32 slots) that fits the budget — two CTAs
+    // per SM when that still covers the source rows `ty` consecutive output rows span plus
+    // two rows of look-ahead; otherwise fewer rows in flight, then one CTA per SM.
     k.sparse = k.y_ratio >= 2.0f ? 1u : 0u;
     auto span_rows = [&](uint32_t g) { return k.sparse ? 2u * g : (uint32_t)((double)(g - 1) * (double)k.y_ratio) + 3; };
-    // Output rows per consumer group: as many as the ring can cover (an extreme
-    // vertical downscale spans many source rows per output row, so the group
-    // shrinks, down to a single row), first within the two-CTAs-per-SM budget.
-    uint32_t group = 0, s_log2 = 0;
+    uint32_t rows_in_flight = 0, s_log2 = 0;
     const size_t budgets[2] = {100 * 1024, (size_t)dev->max_smem_optin};
-    for (int bi = 0; bi < 2 && !group; ++bi) {
+    for (int bi = 0; bi < 2 && !rows_in_flight; ++bi) {
         const size_t avail = budgets[bi] > k.ring_off ? budgets[bi] - k.ring_off : 0;
         const uint32_t slots = (uint32_t)(avail / slot);
-        uint32_t lg = 0;
-        while ((2u << lg) <= slots && lg < 6) ++lg;
         if (slots < 2) continue;
-        for (uint32_t g = ty * 2; g >= 1; g = (g > ty ? ty : g / 2)) {
+        uint32_t lg = 0;
+        while ((2u << lg) <= slots && lg < 5) ++lg;
+        for (uint32_t g = ty; g >= 1; --g) {
             const uint32_t gg = g < k.dst_h ? g : k.dst_h;
-            if ((1u << lg) >= span_rows(gg) + 1) { group = gg; s_log2 = lg; break; }
-            if (g == 1) break;
+            if ((1u << lg) >= span_rows(gg) + (bi == 0 && g > 1 ? 2u : 0u)) { rows_in_flight = gg; s_log2 = lg; break; }
         }
     }
-    if (!group) {
+    if (!rows_in_flight) {
         tk_error_set_detail("source rows of %u bytes do not fit the shared-memory ring", slot);
         return TK_ERROR_NOT_IMPLEMENTED;
     }
     k.s_log2 = s_log2;
-    k.group_rows = group;
+    k.tx = tx; k.ty = rows_in_flight;
     const size_t smem = k.ring_off + ((size_t)slot << s_log2);
+    dim3 block(tx * rows_in_flight + 32);
 
     const unsigned long long total_rows = (unsigned long long)k.num_frames * k.dst_h;
-    unsigned long long max_ctas = (total_rows + group - 1) / group;
+    const unsigned long long per_cta_min = 2ull * rows_in_flight;            // at least two rows per consumer stream
+    unsigned long long max_ctas = (total_rows + per_cta_min - 1) / per_cta_min;
     const uint32_t resident = (smem <= 110 * 1024 ? 2u : 1u) * (uint32_t)dev->sm_count;
     dim3 grid((unsigned)(max_ctas < resident ? max_ctas : resident));
 
