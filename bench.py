@@ -370,7 +370,8 @@ def run_b200(args) -> None:
         step_ach = (ALG_PRE + ALG_POST) * B / (step_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": "frames/s", "n_gpus": world,
                 "steps": K, "warmup": max(W, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(world, B),
+                "vs_baseline": None, "dtype": "f16 lerp -> f16 tensor (pre-process, within the 1e-2 fp16 bar); f32 / i32 (decode, NMS, bit-exact)",
+                "data": "synthetic", "config": config_dict(world, B),
                 "roofline": roofline, "roofline_stages": stages,
                 "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
                                   "unit": "GB/s", "frac": step_ach / peak},

@@ -86,8 +86,11 @@ typedef enum { TK_B200_OUT_F32 = 0, TK_B200_OUT_F16 = 1 } tk_b200_out_type_e;
 typedef enum { TK_B200_RESIZE_STRETCH = 0, TK_B200_RESIZE_LETTERBOX = 1 } tk_b200_resize_mode_e;
 /* EXACT: every fp32 operation of the reference in its order, no contraction;
  *        bit-identical to the reference's AVX build.
- * FAST : lerp form with FMA; within 1e-5 + 1e-5|ref| of the reference. */
-typedef enum { TK_B200_ARITH_EXACT = 0, TK_B200_ARITH_FAST = 1 } tk_b200_arith_e;
+ * FAST : lerp form with FMA; within 1e-5 + 1e-5|ref| of the reference.
+ * HALF : fp16 output only (RGB8 / RGBA8 input; otherwise FAST is used): bytes
+ *        become exact half2 pairs and the lerps run in HFMA2; within the
+ *        1e-2 + 1e-2|ref| fp16 bar of the reference (measured max ~4e-3). */
+typedef enum { TK_B200_ARITH_EXACT = 0, TK_B200_ARITH_FAST = 1, TK_B200_ARITH_HALF = 2 } tk_b200_arith_e;
 typedef enum { TK_B200_ACT_RAW = 0, TK_B200_ACT_SIGMOID = 1, TK_B200_ACT_SOFTMAX = 2 } tk_b200_activation_e;
 
 /* Batched fused pre-process: N frames of one geometry -> [N][3][H][W]. */

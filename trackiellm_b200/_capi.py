@@ -20,7 +20,7 @@ TK_ERROR_INVALID_DIMENSIONS = 5008
 PIXEL_RGB8, PIXEL_RGBA8, PIXEL_I420 = 0, 1, 2
 OUT_F32, OUT_F16 = 0, 1
 RESIZE_STRETCH, RESIZE_LETTERBOX = 0, 1
-ARITH_EXACT, ARITH_FAST = 0, 1
+ARITH_EXACT, ARITH_FAST, ARITH_HALF = 0, 1, 2
 ACT_RAW, ACT_SIGMOID, ACT_SOFTMAX = 0, 1, 2
 
 

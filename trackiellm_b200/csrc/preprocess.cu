@@ -42,6 +42,7 @@ struct PreK {
     float x_ratio, y_ratio;
     float mean[3], stdv[3], rstd[3], fscale[3], fbias[3];
     float pad_value;
+    uint32_t h_scale_rg, h_bias_rg, h_scale_bb, h_bias_bb;   // HALF arithmetic: half2 {R,G} and {B,B} of 1/(255 std), -mean/std
     uint32_t s_log2;        // ring slots = 1 << s_log2
     uint32_t slot_bytes;    // bytes per ring slot (multiple of 16)
     uint32_t copy_bytes;    // bytes per bulk copy of one (luma) row
@@ -190,8 +191,42 @@ __device__ __forceinline__ void warp_copy_unaligned(uint8_t* dst, const uint8_t*
 //              q mod S once q - S < min(progress[*]); lane 0 then issues the TMA bulk
 //              copy (or the warp copies) that completes full[slot].
 // There is no CTA-wide barrier after set-up.
-template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
+// HALF arithmetic (fp16 output, RGB8 / RGBA8): the 2x2 neighbourhood as half2 {R,G} and {B,B}
+// pairs, 0x6400 | byte == 1024 + byte exactly, differences exact, lerps and the
+// normalisation in HFMA2 — half the math instructions of the fp32 lerp.
+template <int FMT>
+__device__ __forceinline__ void fetch_pairs_half(const uint8_t* row, int xb, uint32_t& l_rg, uint32_t& l_bb,
+                                                 uint32_t& r_rg, uint32_t& r_bb) {
+    const uint32_t C64 = 0x64646464u;
+    uint32_t lw, rw;                                   // words starting at the left / right pixel
+    if constexpr (FMT == FMT_RGB8) {
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + (xb & ~3));
+        const uint32_t a0 = a[0], a1 = a[1], a2 = a[2];
+        const uint32_t sh = (uint32_t)xb << 3;
+        lw = __funnelshift_r(a0, a1, sh);
+        rw = __funnelshift_r(lw, __funnelshift_r(a1, a2, sh), 24);
+    } else {
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + xb);
+        lw = a[0]; rw = a[1];
+    }
+    l_rg = __byte_perm(lw, C64, 0x4140); l_bb = __byte_perm(lw, C64, 0x4242);
+    r_rg = __byte_perm(rw, C64, 0x4140); r_bb = __byte_perm(rw, C64, 0x4242);
+}
+__device__ __forceinline__ __half2 as_h2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+__device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ __half2 lerp_pair_half(uint32_t tl, uint32_t tr, uint32_t bl, uint32_t br, __half2 xd2, __half2 yd2) {
+    const __half2 k1024 = as_h2(0x64006400u);
+    const __half2 top = __hfma2(xd2, __hsub2(as_h2(tr), as_h2(tl)), __hsub2(as_h2(tl), k1024));
+    const __half2 bot = __hfma2(xd2, __hsub2(as_h2(br), as_h2(bl)), __hsub2(as_h2(bl), k1024));
+    return __hfma2(yd2, __hsub2(bot, top), top);
+}
+
+enum { AR_EXACT = 0, AR_FAST = 1, AR_HALF = 2 };
+
+template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
+    constexpr bool EXACT = (AR == AR_EXACT);
+    static_assert(AR != AR_HALF || (F16 && FMT != FMT_I420), "HALF arithmetic: fp16 output, RGB8/RGBA8 input");
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);                 // 32 x 8 B
     volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(full + 32);   // one per consumer warp (<= 32)
@@ -221,6 +256,7 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
             xd = __fsub_rn(gx, (float)x);
             xb = (FMT == FMT_RGB8) ? 3 * x : (FMT == FMT_RGBA8 ? 4 * x : x);
         }
+        if constexpr (AR == AR_HALF) xd = __uint_as_float(h2_bits(__float2half2_rn(xd)));   // half2 {xd, xd} bit pattern
         xb_tab[w] = xb; xd_tab[w] = xd;
     }
     __syncthreads();
@@ -339,6 +375,52 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
                 mbar_wait_backoff(&full[q1 & smask], (q1 >> p.s_log2) & 1u);
             }
             for (uint32_t q = cx; q < Q; q += p.tx) {
+                if constexpr (AR == AR_HALF) {
+                    const __half2 yd2 = __float2half2_rn(yd);
+                    const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                    const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                    uint32_t org[4], obb[4];
+                    if (vin) {
+                        const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+                        const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
+                        const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
+                        const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
+                            uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
+                            fetch_pairs_half<FMT>(row0, xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
+                            fetch_pairs_half<FMT>(row1, xbs[j], bl_rg, bl_bb, br_rg, br_bb);
+                            const __half2 xd2 = as_h2(xds[j]);
+                            org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                            obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
+                    }
+                    // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
+                    const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
+                    const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
+                    const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
+                    const size_t pix = (size_t)h * p.dst_w + 4u * q;
+                    __half* outp = static_cast<__half*>(p.out);
+                    const uint2 vs[3] = {vr, vg, vb};
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const size_t e = ((size_t)f * 3 + c) * plane + pix;
+                        if (p.vec_store) {
+                            __stcs(reinterpret_cast<uint2*>(outp + e), vs[c]);
+                        } else {
+                            const uint32_t wds[2] = {vs[c].x, vs[c].y};
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (4u * q + j < p.dst_w)
+                                    reinterpret_cast<uint16_t*>(outp)[e + j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                        }
+                    }
+                    continue;
+                }
                 float o[3][4];
                 if (vin) {
                     const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
@@ -430,28 +512,32 @@ void letterbox_geometry(uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh,
     *pt = (dh - *nh) / 2;
 }
 
-template <int FMT, bool F16, bool EXACT, bool LBOX, bool TMA>
+template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 static tk_error_code_t launch_variant(const PreK& k, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
-    auto kern = preprocess_kernel<FMT, F16, EXACT, LBOX, TMA>;
+    auto kern = preprocess_kernel<FMT, F16, AR, LBOX, TMA>;
     TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     kern<<<grid, block, smem, stream>>>(k);
     return launch_status("preprocess_kernel");
 }
 
-template <int FMT, bool F16, bool EXACT>
+template <int FMT, bool F16, int AR>
 static tk_error_code_t launch_fmt(const PreK& k, bool lbox, bool tma, dim3 g, dim3 b, size_t s, cudaStream_t st) {
-    if (lbox) return tma ? launch_variant<FMT, F16, EXACT, true, true>(k, g, b, s, st)
-                         : launch_variant<FMT, F16, EXACT, true, false>(k, g, b, s, st);
-    return tma ? launch_variant<FMT, F16, EXACT, false, true>(k, g, b, s, st)
-               : launch_variant<FMT, F16, EXACT, false, false>(k, g, b, s, st);
+    if (lbox) return tma ? launch_variant<FMT, F16, AR, true, true>(k, g, b, s, st)
+                         : launch_variant<FMT, F16, AR, true, false>(k, g, b, s, st);
+    return tma ? launch_variant<FMT, F16, AR, false, true>(k, g, b, s, st)
+               : launch_variant<FMT, F16, AR, false, false>(k, g, b, s, st);
 }
 
 template <int FMT>
-static tk_error_code_t launch_type(const PreK& k, bool f16, bool exact, bool lbox, bool tma, dim3 g, dim3 b, size_t s, cudaStream_t st) {
-    if (f16) return exact ? launch_fmt<FMT, true, true>(k, lbox, tma, g, b, s, st)
-                          : launch_fmt<FMT, true, false>(k, lbox, tma, g, b, s, st);
-    return exact ? launch_fmt<FMT, false, true>(k, lbox, tma, g, b, s, st)
-                 : launch_fmt<FMT, false, false>(k, lbox, tma, g, b, s, st);
+static tk_error_code_t launch_type(const PreK& k, bool f16, int ar, bool lbox, bool tma, dim3 g, dim3 b, size_t s, cudaStream_t st) {
+    if constexpr (FMT != FMT_I420) {
+        if (f16 && ar == AR_HALF) return launch_fmt<FMT, true, AR_HALF>(k, lbox, tma, g, b, s, st);
+    }
+    if (ar == AR_HALF) ar = AR_FAST;                   // I420 or fp32 output: the fp32 lerp
+    if (f16) return ar == AR_EXACT ? launch_fmt<FMT, true, AR_EXACT>(k, lbox, tma, g, b, s, st)
+                                   : launch_fmt<FMT, true, AR_FAST>(k, lbox, tma, g, b, s, st);
+    return ar == AR_EXACT ? launch_fmt<FMT, false, AR_EXACT>(k, lbox, tma, g, b, s, st)
+                          : launch_fmt<FMT, false, AR_FAST>(k, lbox, tma, g, b, s, st);
 }
 
 }  // namespace tkb
@@ -504,6 +590,14 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
         k.fbias[c] = (float)(-(double)mu / (double)sd);
     }
     k.pad_value = prm->pad_value;
+    {
+        auto h2 = [](float lo, float hi) {
+            __half2 v = __floats2half2_rn(lo, hi);
+            uint32_t u; memcpy(&u, &v, 4); return u;
+        };
+        k.h_scale_rg = h2(k.fscale[0], k.fscale[1]); k.h_bias_rg = h2(k.fbias[0], k.fbias[1]);
+        k.h_scale_bb = h2(k.fscale[2], k.fscale[2]); k.h_bias_bb = h2(k.fbias[2], k.fbias[2]);
+    }
     unsigned long long frame_bytes = (unsigned long long)k.src_stride * k.src_h;
     if (fmt == FMT_I420) {
         if (k.src_w < 4 || k.src_h < 4) return TK_ERROR_INVALID_DIMENSIONS;
@@ -576,11 +670,12 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     dim3 grid((unsigned)(max_ctas < resident ? max_ctas : resident));
 
     const bool f16 = prm->output_type == TK_B200_OUT_F16;
-    const bool exact = prm->arith == TK_B200_ARITH_EXACT;
+    if ((unsigned)prm->arith > TK_B200_ARITH_HALF) return TK_ERROR_INVALID_ARGUMENT;
+    const int ar = (int)prm->arith;
     switch (fmt) {
-        case FMT_RGB8:  return launch_type<FMT_RGB8>(k, f16, exact, lbox, tma, grid, block, smem, stream);
-        case FMT_RGBA8: return launch_type<FMT_RGBA8>(k, f16, exact, lbox, tma, grid, block, smem, stream);
-        default:        return launch_type<FMT_I420>(k, f16, exact, lbox, tma, grid, block, smem, stream);
+        case FMT_RGB8:  return launch_type<FMT_RGB8>(k, f16, ar, lbox, tma, grid, block, smem, stream);
+        case FMT_RGBA8: return launch_type<FMT_RGBA8>(k, f16, ar, lbox, tma, grid, block, smem, stream);
+        default:        return launch_type<FMT_I420>(k, f16, ar, lbox, tma, grid, block, smem, stream);
     }
 }
 

@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import _capi as capi
-from ._capi import (ACT_RAW, ACT_SIGMOID, ACT_SOFTMAX, ARITH_EXACT, ARITH_FAST, OUT_F16, OUT_F32,
+from ._capi import (ACT_RAW, ACT_SIGMOID, ACT_SOFTMAX, ARITH_EXACT, ARITH_FAST, ARITH_HALF, OUT_F16, OUT_F32,
                     PIXEL_I420, PIXEL_RGB8, PIXEL_RGBA8, RESIZE_LETTERBOX, RESIZE_STRETCH)
 
 IMAGENET_MEAN = (0.485, 0.456, 0.406)   # src/vision/tk_object_detector.c:248
@@ -62,7 +62,7 @@ def preprocess_batch(frames: torch.Tensor, out_w: int, out_h: int, *, width: int
     pitch = frames.stride(0) * frames.element_size()
     f16 = out_dtype == torch.float16
     if arith is None:
-        arith = ARITH_FAST if f16 else ARITH_EXACT
+        arith = ARITH_HALF if f16 else ARITH_EXACT     # HALF falls back to FAST inside the library for I420
     if out is None:
         out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=frames.device)
     p = capi.PreprocessBatchParams(
@@ -327,7 +327,7 @@ class Pipeline:
                  stage_host_logits: bool = False):
         f16 = out_dtype == torch.float16
         if arith is None:
-            arith = ARITH_FAST if f16 else ARITH_EXACT
+            arith = ARITH_HALF if f16 else ARITH_EXACT
         self.cfg = capi.PipelineConfig(
             device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, input_width=width,
             input_height=height, input_stride_bytes=stride, input_format=fmt, tensor_width=tensor_w,
