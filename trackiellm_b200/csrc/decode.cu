@@ -17,7 +17,10 @@
 //     every CTA its exclusive offset inside the frame: the output is in
 //     ascending proposal order with no atomics and no second launch.
 //   * Pass 2: one warp per surviving row loads the whole row coalesced, finds
-//     the first-max class by shuffle reduction, and writes the 28-byte record.
+//     the first-max class by shuffle reduction, and stages the 28-byte record in
+//     shared memory in row order; the cluster barrier is split (arrive before
+//     pass 2, wait after it) so the exchange hides behind the row decode, and the
+//     staged records leave as one coalesced word copy.
 //   * Sigmoid / softmax use tk_dm_expf (include/tk_b200_detmath.h), the same
 //     source the oracle compiles, so thresholds and scores agree bit for bit.
 #include "tk_common.cuh"
@@ -48,27 +51,79 @@ __device__ __forceinline__ float act_fn(float x) {
     else return tk_dm_sigmoidf(x);
 }
 
-// (value, index) pairs for the reference's sequential first-max scan
-//   best = 0; for j >= 1: if (v[j] > v[best]) best = j;
-// i == kNone means "no element".  Only element 0 can carry a NaN value (NaNs at
-// j >= 1 never win a `>` and are dropped when read); a NaN at element 0 is never
-// displaced, exactly as in the sequential scan.
 static constexpr uint32_t kNone = 0xffffffffu;
-__device__ __forceinline__ void amax_combine(float& v, uint32_t& i, float ov, uint32_t oi) {
-    if (oi == kNone) return;
-    if (i == kNone) { v = ov; i = oi; return; }
-    if (v != v) return;                       // NaN at element 0 stays
-    if (ov != ov) { v = ov; i = oi; return; }
-    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+
+// Objectness load of pass 1: 4 bytes out of every 340-byte row.  The L2::64B hint
+// halves the DRAM fetch per row (the default fetches 128 B): 33 -> 25 us for
+// 64 x 25200 rows (tools/exp_stride.cu).
+__device__ __forceinline__ float ld_obj(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::64B.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
 }
 
+static constexpr uint32_t kDecStage = 256;     // candidate records a CTA stages in shared memory (7 KB)
+static constexpr int kDecUnroll = 8;           // objectness loads in flight per thread
+
 template <int ACT>
-__global__ void __launch_bounds__(kDecThreads) decode_kernel(const DecK k) {
+__device__ __forceinline__ tk_b200_candidate_t decode_row(const DecK& k, const float* row, uint32_t r, uint32_t lane, float* my_e) {
+    // First-max class over raw logits: the reference's sequential scan
+    //   best = 0; for j >= 1: if (v[j] > v[best]) best = j;      (tie rule of tk_attribute_classifier.c:83-88)
+    // as two warp reductions on order-preserving integer keys.  -0 and +0 compare equal
+    // (canonicalised by + 0.0f), a NaN at j >= 1 never wins (key 0, below every number),
+    // a NaN at j == 0 is never displaced (key 0xffffffff); ties -> lowest index.
+    uint32_t lk = 0, li = kNone; float lv = 0.0f;
+    for (uint32_t j = lane; j < k.C; j += 32) {
+        const float v = __ldg(row + 5 + j);
+        const uint32_t key = (v != v) ? (j == 0 ? 0xffffffffu : 0u) : tk_dm_float_order_key(__fadd_rn(v, 0.0f));
+        if (li == kNone || key > lk) { lk = key; li = j; lv = v; }
+    }
+    const uint32_t mk = __reduce_max_sync(0xffffffffu, lk);
+    const uint32_t bidx = __reduce_min_sync(0xffffffffu, (li != kNone && lk == mk) ? li : kNone);
+    const uint32_t best = (bidx == kNone) ? 0u : bidx;
+    const float bestv = __shfl_sync(0xffffffffu, lv, best & 31u);  // lane (best mod 32) owns class `best`
+    float cls = 0.0f;
+    if (k.C == 0) cls = 1.0f;
+    else if constexpr (ACT == TK_B200_ACT_RAW) cls = bestv;
+    else if constexpr (ACT == TK_B200_ACT_SIGMOID) cls = tk_dm_sigmoidf(bestv);
+    else {
+        // class softmax in the arithmetic order of tests/tk_gpu_softmax_test.cpp:31-49:
+        // exponentials in parallel, the sum strictly in index order.
+        for (uint32_t j = lane; j < k.C; j += 32) my_e[j] = tk_dm_expf(__fsub_rn(__ldg(row + 5 + j), bestv));
+        __syncwarp();
+        float sum = 0.0f;
+        if (lane == 0) {
+            for (uint32_t j = 0; j < k.C; ++j) sum = __fadd_rn(sum, my_e[j]);
+            cls = __fdiv_rn(tk_dm_expf(__fsub_rn(bestv, bestv)), sum);
+        }
+        __syncwarp();
+    }
+    tk_b200_candidate_t c;
+    // lanes 0..4 hold cx, cy, w, h, objectness
+    const float head = lane < 5 ? __ldg(row + lane) : 0.0f;
+    const float cx = __shfl_sync(0xffffffffu, head, 0), cy = __shfl_sync(0xffffffffu, head, 1);
+    const float bw = __shfl_sync(0xffffffffu, head, 2), bh = __shfl_sync(0xffffffffu, head, 3);
+    const float obj = act_fn<ACT>(__shfl_sync(0xffffffffu, head, 4));
+    c.index = (int32_t)r;
+    c.bbox.x = __float2int_rz(__fsub_rn(cx, __fmul_rn(bw, 0.5f)));   // :347  (int)(cx - w/2)
+    c.bbox.y = __float2int_rz(__fsub_rn(cy, __fmul_rn(bh, 0.5f)));   // :348
+    c.bbox.w = __float2int_rz(bw);                                    // :349
+    c.bbox.h = __float2int_rz(bh);                                    // :350
+    c.confidence = tk_dm_canon_nan(__fmul_rn(obj, cls));             // valid on lane 0 (cls)
+    c.class_id = best;
+    return c;
+}
+
+// 4 CTAs per SM (<= 32 registers): with 3, only 48 of the 64 clusters of the bench batch are
+// co-resident (a cluster of 8 must sit in one GPC) and the launch needs two waves.
+template <int ACT>
+__global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
     extern __shared__ __align__(16) uint8_t dsm[];
     uint32_t* flags = reinterpret_cast<uint32_t*>(dsm);            // [nwords] ballot bitmap
     uint32_t* wpre = flags + k.nwords;                             // [nwords] exclusive prefix of popc
     float* ebuf = reinterpret_cast<float*>(wpre + k.nwords);       // softmax only: [warps][C]
     __shared__ uint32_t cta_tot[kDecCluster];                      // filled by every CTA of the cluster
+    __shared__ uint32_t stage[kDecStage * 7];                      // this CTA's first kDecStage records, in row order
 
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t rank = cluster.block_rank();
@@ -78,27 +133,32 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const DecK k) {
     const uint32_t row0 = rank * k.rows_per_cta;
 
     // ---- pass 1: objectness threshold, ballot bitmap ------------------------
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");   // "I am resident" (waited on before DSMEM)
-    for (uint32_t base = 0; base < k.rows_per_cta; base += 4 * kDecThreads) {
-        float obj[4];
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // "I am resident" (waited on before DSMEM)
+    for (uint32_t base = 0; base < k.rows_per_cta; base += kDecUnroll * kDecThreads) {
+        float obj[kDecUnroll];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            uint32_t r = row0 + base + u * kDecThreads + tid;
-            uint32_t lr = base + u * kDecThreads + tid;
-            obj[u] = (lr < k.rows_per_cta && r < k.P) ? __ldg(fl + (size_t)r * k.L + 4) : __int_as_float(0x7fc00000);
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const uint32_t lr = base + u * kDecThreads + tid, r = row0 + lr;
+            obj[u] = (lr < k.rows_per_cta && r < k.P) ? ld_obj(fl + (size_t)r * k.L + 4) : __int_as_float(0x7fc00000);
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            uint32_t lr = base + u * kDecThreads + tid;
-            bool pass = act_fn<ACT>(obj[u]) > k.thr;               // NaN never passes
-            uint32_t b = __ballot_sync(0xffffffffu, pass);
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const uint32_t lr = base + u * kDecThreads + tid;
+            const bool pass = act_fn<ACT>(obj[u]) > k.thr;         // NaN never passes
+            if (pass) {
+                // pull the surviving row towards L2 now; pass 2 reads it a few microseconds later
+                const char* rp = reinterpret_cast<const char*>(fl + (size_t)(row0 + lr) * k.L);
+                const uint32_t rb = k.L * 4;
+                for (uint32_t o = 0; o < rb; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + o));
+            }
+            const uint32_t b = __ballot_sync(0xffffffffu, pass);
             if (lane == 0 && lr < k.rows_per_cta) flags[lr >> 5] = b;
         }
     }
     __syncthreads();
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");     // every peer CTA has started
+    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");             // every peer CTA has started
 
-    // ---- exclusive prefix over the bitmap words + cluster exchange ----------
+    // ---- exclusive prefix over the bitmap words; totals to every peer through DSMEM ----
     if (warp == 0) {
         uint32_t run = 0;
         for (uint32_t w0 = 0; w0 < k.nwords; w0 += 32) {
@@ -116,7 +176,33 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const DecK k) {
         if (lane < kDecCluster)
             *cluster.map_shared_rank(&cta_tot[rank], lane) = run;  // DSMEM store into every peer
     }
-    cluster.sync();
+    __syncthreads();
+    // The frame-level offset is only needed to write the records out: arrive now, wait after
+    // the rows are decoded, so the cluster exchange hides behind pass 2.
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+
+    // ---- pass 2: one warp per surviving row, records staged in shared memory in row order ----
+    // Survivor s of this CTA goes to warp s mod 16 (balanced however the survivors cluster);
+    // its row is found by binary search in the word prefix + select inside the word.
+    float* my_e = ebuf + (size_t)warp * k.C;
+    const uint32_t local_n = __popc(flags[k.nwords - 1]) + wpre[k.nwords - 1];
+    for (uint32_t sidx = warp; sidx < min(local_n, kDecStage); sidx += kDecWarps) {
+        uint32_t lo = 0, hi = k.nwords - 1;                        // last word with wpre[w] <= sidx
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            if (wpre[mid] <= sidx) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t b = __fns(flags[lo], 0, (int)(sidx - wpre[lo]) + 1);
+        const uint32_t r = row0 + lo * 32 + b;
+        const tk_b200_candidate_t c = decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e);
+        if (lane == 0) {
+            uint32_t* sp = stage + sidx * 7;
+            sp[0] = (uint32_t)c.index; sp[1] = (uint32_t)c.bbox.x; sp[2] = (uint32_t)c.bbox.y; sp[3] = (uint32_t)c.bbox.w;
+            sp[4] = (uint32_t)c.bbox.h; sp[5] = __float_as_uint(c.confidence); sp[6] = c.class_id;
+        }
+    }
+    __syncthreads();
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     uint32_t frame_pre = 0, frame_tot = 0;
 #pragma unroll
     for (int r = 0; r < kDecCluster; ++r) {
@@ -125,62 +211,30 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const DecK k) {
         frame_tot += t;
     }
     if (rank == 0 && tid == 0) k.counts[frame] = frame_tot;
+    const uint32_t local_tot = cta_tot[rank];
 
-    // ---- pass 2: one warp per surviving row ---------------------------------
+    // ---- write-out: the staged records are one contiguous, coalesced word copy ----
     tk_b200_candidate_t* out = k.cands + (size_t)frame * k.cap;
-    float* my_e = ebuf + (size_t)warp * k.C;
-    for (uint32_t w = warp; w < k.nwords; w += kDecWarps) {
-        const uint32_t word = flags[w];
-        uint32_t bits = word;
-        while (bits) {
-            const uint32_t b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const uint32_t pos = frame_pre + wpre[w] + __popc(word & ((1u << b) - 1u));
-            if (pos >= k.cap) { bits = 0; break; }                 // later rows only have larger pos
-            const uint32_t r = row0 + w * 32 + b;
-            const float* row = fl + (size_t)r * k.L;
-            // first-max class over raw logits (tie rule of tk_attribute_classifier.c:83-88)
-            float bv = 0.0f; uint32_t bi = kNone;
-            for (uint32_t j = lane; j < k.C; j += 32) {
-                float v = __ldg(row + 5 + j);
-                if (j == 0 || v == v) amax_combine(bv, bi, v, j);
-            }
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) {
-                float ov = __shfl_xor_sync(0xffffffffu, bv, d);
-                uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, d);
-                amax_combine(bv, bi, ov, oi);
-            }
-            const uint32_t best = (bi == kNone) ? 0u : bi;
-            const float bestv = bv;
-            float cls = 0.0f;
-            if (k.C == 0) cls = 1.0f;
-            else if constexpr (ACT == TK_B200_ACT_RAW) cls = bestv;
-            else if constexpr (ACT == TK_B200_ACT_SIGMOID) cls = tk_dm_sigmoidf(bestv);
-            else {
-                // class softmax in the arithmetic order of tests/tk_gpu_softmax_test.cpp:31-49:
-                // exponentials in parallel, the sum strictly in index order.
-                for (uint32_t j = lane; j < k.C; j += 32) my_e[j] = tk_dm_expf(__fsub_rn(__ldg(row + 5 + j), bestv));
-                __syncwarp();
-                float sum = 0.0f;
-                if (lane == 0) {
-                    for (uint32_t j = 0; j < k.C; ++j) sum = __fadd_rn(sum, my_e[j]);
-                    cls = __fdiv_rn(tk_dm_expf(__fsub_rn(bestv, bestv)), sum);
-                }
-                __syncwarp();
-            }
-            if (lane == 0) {
-                float cx = __ldg(row + 0), cy = __ldg(row + 1), bw = __ldg(row + 2), bh = __ldg(row + 3);
-                float obj = act_fn<ACT>(__ldg(row + 4));
-                tk_b200_candidate_t c;
-                c.index = (int32_t)r;
-                c.bbox.x = __float2int_rz(__fsub_rn(cx, __fmul_rn(bw, 0.5f)));   // :347  (int)(cx - w/2)
-                c.bbox.y = __float2int_rz(__fsub_rn(cy, __fmul_rn(bh, 0.5f)));   // :348
-                c.bbox.w = __float2int_rz(bw);                                    // :349
-                c.bbox.h = __float2int_rz(bh);                                    // :350
-                c.confidence = tk_dm_canon_nan(__fmul_rn(obj, cls));
-                c.class_id = best;
-                out[pos] = c;
+    if (frame_pre < k.cap) {
+        const uint32_t nrec = min(min(local_tot, kDecStage), k.cap - frame_pre);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(out + frame_pre);
+        for (uint32_t i = tid; i < nrec * 7; i += kDecThreads) dst[i] = stage[i];
+    }
+    // ---- overflow (more than kDecStage survivors in this CTA's slice): straight to global ----
+    if (local_tot > kDecStage) {
+        for (uint32_t w = warp; w < k.nwords; w += kDecWarps) {
+            const uint32_t word = flags[w];
+            uint32_t bits = word;
+            while (bits) {
+                const uint32_t b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const uint32_t lpos = wpre[w] + __popc(word & ((1u << b) - 1u));
+                if (lpos < kDecStage) continue;
+                const uint32_t pos = frame_pre + lpos;
+                if (pos >= k.cap) { bits = 0; break; }             // later rows only have larger pos
+                const uint32_t r = row0 + w * 32 + b;
+                const tk_b200_candidate_t c = decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e);
+                if (lane == 0) out[pos] = c;
             }
         }
     }
