@@ -83,6 +83,38 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* keys, uint32_t*
     }
 }
 
+// Bitonic sort of 512 (key, payload) pairs held one per thread: partner distances below
+// 32 are warp shuffles, the 10 larger ones go through shared memory (two buffers used
+// alternately: one CTA barrier per exchange).  35 of the 45 stages need no barrier.
+template <bool PAYLOAD>
+__device__ __forceinline__ void bitonic_sort_regs512(unsigned long long& key, uint32_t& pay, unsigned long long* xk0,
+                                                     unsigned long long* xk1, uint32_t* xp0, uint32_t* xp1, uint32_t tid) {
+    uint32_t flip = 0;
+#pragma unroll
+    for (uint32_t kk = 2; kk <= 512; kk <<= 1) {
+#pragma unroll
+        for (uint32_t j = kk >> 1; j > 0; j >>= 1) {
+            unsigned long long ok; uint32_t op = 0;
+            if (j >= 32) {
+                unsigned long long* xk = flip ? xk1 : xk0;
+                uint32_t* xp = flip ? xp1 : xp0;
+                flip ^= 1u;
+                xk[tid] = key;
+                if (PAYLOAD) xp[tid] = pay;
+                __syncthreads();
+                ok = xk[tid ^ j];
+                if (PAYLOAD) op = xp[tid ^ j];
+            } else {
+                ok = __shfl_xor_sync(0xffffffffu, key, j);
+                if (PAYLOAD) op = __shfl_xor_sync(0xffffffffu, pay, j);
+            }
+            const bool take_min = ((tid & j) == 0) == ((tid & kk) == 0);
+            const bool swap = take_min ? (ok < key) : (ok > key);
+            if (swap) { key = ok; pay = op; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
     extern __shared__ __align__(16) uint8_t dsm[];
     __shared__ unsigned long long diag[64];
@@ -107,6 +139,38 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
     unsigned long long* keys2 = reinterpret_cast<unsigned long long*>(dead + k.Kp); // [Kp] (class << 32 | score rank)
     unsigned long long* segmask = keys2 + k.Kp;                                     // [Kp] class order
 
+    if (tid < kNmsMaxK / 64) keptbits[tid] = 0ull;
+    if (tid == 0) seg_overflow = 0;
+    if (Kp <= 512) {
+        // ---- register path: one candidate per thread, both sorts mostly in shuffles ----
+        unsigned long long key = ~0ull; uint32_t p0 = tid;
+        if (tid < K) {
+            uint32_t ck = tk_dm_float_order_key(in[tid].confidence);
+            key = ((unsigned long long)(~ck) << 32) | (uint32_t)in[tid].index;
+        }
+        // ascending key == confidence desc, index asc.  Equal keys (same confidence and
+        // same index) can only be distinct input positions holding identical proposals;
+        // any order among them gives the same output.
+        bitonic_sort_regs512<true>(key, p0, keys, keys2, pos, cls, tid);
+        __syncthreads();                                           // exchange buffers (pos, cls) are free again
+        unsigned long long k2 = ~0ull;
+        if (tid < K) {
+            const tk_b200_candidate_t& c = in[p0];
+            box[tid] = make_int4(c.bbox.x, c.bbox.y, c.bbox.w, c.bbox.h);
+            const uint32_t cc = k.agnostic ? 0u : c.class_id;
+            k2 = ((unsigned long long)cc << 32) | tid;
+        }
+        const uint32_t my_cls = (uint32_t)(k2 >> 32);
+        uint32_t none = 0;
+        // Second sort groups each class into one contiguous segment, score order inside
+        // (a class id of 0xffffffff sorts with the padding but keeps a rank < K, so it is
+        // told apart below by t < K).
+        bitonic_sort_regs512<false>(k2, none, keys, keys2, nullptr, nullptr, tid);
+        __syncthreads();
+        if (tid < K) { pos[tid] = p0; cls[tid] = my_cls; dead[tid] = 0; }
+        keys2[tid] = k2;
+        __syncthreads();
+    } else {
     // ---- score keys -----------------------------------------------------------
     for (uint32_t i = tid; i < Kp; i += kNmsThreads) {
         unsigned long long key = ~0ull;
@@ -116,12 +180,7 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
         }
         keys[i] = key; pos[i] = i;
     }
-    if (tid < kNmsMaxK / 64) keptbits[tid] = 0ull;
-    if (tid == 0) seg_overflow = 0;
     __syncthreads();
-    // ascending key == confidence desc, index asc.  Equal keys (same confidence and
-    // same index) can only be distinct input positions holding identical proposals;
-    // any order among them gives the same output.
     bitonic_sort<true>(keys, pos, Kp, tid);
 
     // ---- stage in score order; class keys -----------------------------------------
@@ -137,10 +196,8 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
         keys2[i] = k2;
     }
     __syncthreads();
-    // Second sort groups each class into one contiguous segment, score order inside
-    // (a class id of 0xffffffff sorts with the padding but keeps a rank < K, so it is
-    // told apart below by t < K).
     bitonic_sort<false>(keys2, nullptr, Kp, tid);
+    }
 
     // ---- A. per-candidate suppressor mask inside its class segment -----------------
     // Suppression never crosses classes.  For the candidate at class-order position t
@@ -309,7 +366,7 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
     NmsK k{};
     k.cands = p->d_candidates; k.counts = p->d_counts; k.dets = p->d_detections; k.num_dets = p->d_num_detections;
     k.cap = p->max_candidates; k.max_det = p->max_detections;
-    k.Kp = 64; while (k.Kp < k.cap) k.Kp <<= 1;
+    k.Kp = 512; while (k.Kp < k.cap) k.Kp <<= 1;    // >= 512: the register sort exchanges through 512-entry buffers
     k.thr = p->iou_threshold; k.agnostic = p->class_agnostic;
     const bool any_restore = p->restore_src_width || p->restore_src_height || p->restore_in_width || p->restore_in_height;
     if (any_restore) {
