@@ -1,0 +1,65 @@
+"""Batch / geometry sweep of the device-resident step and of the pre-process kernel alone
+(BASELINE.json configs 4 and 5).  Prints a markdown table; run on the GPU box."""
+import sys, time
+import numpy as np, torch
+sys.path.insert(0, "."); sys.path.insert(0, "tests")
+import synth
+from trackiellm_b200 import vision as V
+
+PEAK = 6538.0
+
+
+def time_us(fn, iters):
+    for _ in range(3):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / iters
+
+
+def pre_geometry():
+    print("| input | output | batch | us/launch | frames/s | algorithmic GB/s | % of 6538 |")
+    print("|---|---|---|---|---|---|---|")
+    for name, w, h, fmt, dt in (("1080p RGB8", 1920, 1080, V.PIXEL_RGB8, torch.float16), ("1080p RGB8", 1920, 1080, V.PIXEL_RGB8, torch.float32),
+                                ("640x480 RGB8", 640, 480, V.PIXEL_RGB8, torch.float32), ("4K RGB8", 3840, 2160, V.PIXEL_RGB8, torch.float16),
+                                ("4K I420", 3840, 2160, V.PIXEL_I420, torch.float16), ("4K I420", 3840, 2160, V.PIXEL_I420, torch.float32)):
+        n = 32
+        fb = w * h * 3 if fmt == V.PIXEL_RGB8 else w * h * 3 // 2
+        fr = torch.randint(0, 256, (n, fb), dtype=torch.uint8, device="cuda")
+        out = torch.empty((n, 3, 640, 640), dtype=dt, device="cuda")
+        us = time_us(lambda: V.preprocess_batch(fr, 640, 640, width=w, height=h, fmt=fmt, out_dtype=dt, out=out), 50)
+        alg = n * (fb + 640 * 640 * 3 * out.element_size())
+        print(f"| {name} | 640x640 {'fp16' if dt == torch.float16 else 'fp32 (EXACT)'} | {n} | {us:.1f} | {n / us * 1e6:.0f} | {alg / us / 1e3:.0f} | {alg / us / 1e3 / PEAK * 100:.1f} |")
+
+
+def batch_sweep():
+    print("\n| batch | step us | frames/s | pre us | decode us | nms us |")
+    print("|---|---|---|---|---|---|")
+    base_f = torch.randint(0, 256, (64, 1080, 1920, 3), dtype=torch.uint8, device="cuda")
+    lg = np.stack([synth.logits_tensor(i) for i in range(8)])
+    base_l = torch.from_numpy(np.concatenate([lg] * 8)).cuda()
+    for b in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024):
+        reps = (b + 63) // 64
+        fr = base_f.repeat(reps, 1, 1, 1)[:b].contiguous() if b > 64 else base_f[:b]
+        ll = base_l.repeat(reps, 1, 1)[:b].contiguous() if b > 64 else base_l[:b]
+        pipe = V.Pipeline(max_batch=b)
+        t, d, c = pipe.alloc_outputs(b)
+        iters = 100 if b <= 64 else 20
+        for _ in range(3):
+            pipe.process_device(fr, ll, t, d, c)
+        torch.cuda.synchronize()
+        pipe.stage_timing(iters)
+        us = time_us(lambda: pipe.process_device(fr, ll, t, d, c), iters)
+        ms, n = pipe.stage_times()
+        pipe.stage_timing(0)
+        print(f"| {b} | {us:.1f} | {b / us * 1e6:.0f} | {ms[0] / n * 1e3:.1f} | {ms[1] / n * 1e3:.1f} | {ms[2] / n * 1e3:.1f} |")
+        pipe.close(); del t, d, c, fr, ll
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    pre_geometry()
+    batch_sweep()
