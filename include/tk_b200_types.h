@@ -115,7 +115,10 @@ typedef enum {
     TK_PIXEL_FORMAT_RGBA8 = 1,
     /* Additive: planar I420 container of src/ffi/c_api/tk_ffi_api.c:917-931
      * (Y w*h, then U, then V, (w/2)*(h/2) each, one allocation). */
-    TK_PIXEL_FORMAT_I420  = 2
+    TK_PIXEL_FORMAT_I420  = 2,
+    /* Additive: packed B,G,R byte order (TK_VISION_FMT_BGR24 of the FFI frame
+     * container, src/ffi/c_api/tk_ffi_api.h).  The tensor planes stay R, G, B. */
+    TK_PIXEL_FORMAT_BGR8  = 3
 } tk_pixel_format_e;
 
 typedef struct tk_video_frame_s {

@@ -200,6 +200,42 @@ typedef struct {
 
 TK_NODISCARD tk_error_code_t tk_kernels_door_state(const tk_b200_door_params_t* params, cudaStream_t stream);
 
+/* MiDaS inverse depth -> metric depth for a batch of maps
+ * (convert_inverse_depth_to_metric, src/vision/tk_depth_midas.c:473-499; the
+ * reference passes TK_DEPTH_ESTIMATOR_MIN/MAX_DEPTH = 0.1 / 10.0, :46-47).
+ * Each map is normalised by its own min/max.  In place (same pointer) is
+ * allowed for maps of up to 196608 elements. */
+typedef struct {
+    const float* d_inverse_depth;   /* [num_maps][height][width]  */
+    float*       d_metric_depth;    /* [num_maps][height][width]  */
+    uint32_t     num_maps;
+    uint32_t     width, height;
+    float        min_depth, max_depth;
+} tk_b200_depth_metric_params_t;
+
+TK_NODISCARD tk_error_code_t tk_kernels_inverse_depth_to_metric(const tk_b200_depth_metric_params_t* params, cudaStream_t stream);
+
+/* Per-detection distance from a metric depth map (calculate_raw_distance,
+ * src/vision/src/object_analysis.rs:227-279): bbox -> depth-map window ->
+ * samples with 0.1 < d < 100 -> sort -> IQR fence -> mean; -1.0 when the
+ * window is degenerate or holds fewer than 10 valid samples.  Bit-identical
+ * to the sequential fp32 reference.  Frame f uses depth map f. */
+typedef struct {
+    const tk_b200_candidate_t* d_detections;     /* [N][max_detections] (bbox in frame px)   */
+    const uint32_t*            d_num_detections; /* [N] or NULL = max_detections everywhere  */
+    uint32_t                   num_frames;       /* N <= 65535                               */
+    uint32_t                   max_detections;
+    const float*               d_depth_maps;     /* [N][depth_height][depth_width]           */
+    uint32_t                   depth_width, depth_height;
+    uint32_t                   frame_width, frame_height;   /* px space of the boxes        */
+    float*                     d_distances;      /* [N][max_detections]; unused slots = -1   */
+    void*                      d_workspace;      /* needed when depth_width*depth_height > 16384 */
+    size_t                     workspace_bytes;  /* >= tk_b200_detection_distance_workspace_bytes */
+} tk_b200_distance_params_t;
+
+size_t tk_b200_detection_distance_workspace_bytes(uint32_t depth_width, uint32_t depth_height);
+TK_NODISCARD tk_error_code_t tk_kernels_detection_distance(const tk_b200_distance_params_t* params, cudaStream_t stream);
+
 /* ------------------------------------------------------------------------ */
 /* Batched pipeline: pre-process + decode + class-wise NMS for a batch of     */
 /* frames of one geometry (the step BASELINE.json's metric counts).  The      */

@@ -163,6 +163,25 @@ def door_state(frame: np.ndarray, bbox) -> tuple[int, int]:
     return int(k), int(cnt.value)
 
 
+def inverse_depth_to_metric(inv: np.ndarray, min_depth: float = 0.1, max_depth: float = 10.0) -> np.ndarray:
+    """One map; src/vision/tk_depth_midas.c:473-499 with its defaults :46-47."""
+    inv = np.ascontiguousarray(inv, np.float32)
+    out = np.empty_like(inv)
+    lib().oracle_inverse_depth_to_metric(_p(inv), _p(out), C.c_size_t(inv.size), C.c_float(min_depth), C.c_float(max_depth))
+    return out
+
+
+def detection_distance(bbox, depth: np.ndarray, frame_w: int, frame_h: int) -> float:
+    """src/vision/src/object_analysis.rs:227-279 for one bbox (x, y, w, h) and one depth map [H][W]."""
+    depth = np.ascontiguousarray(depth, np.float32)
+    scratch = np.empty(depth.size, np.float32)
+    fn = lib().oracle_detection_distance
+    fn.restype = C.c_float
+    x, y, w, h = (int(v) for v in bbox)
+    return float(fn(C.c_int(x), C.c_int(y), C.c_int(w), C.c_int(h), _p(depth), C.c_uint32(depth.shape[1]),
+                    C.c_uint32(depth.shape[0]), C.c_uint32(frame_w), C.c_uint32(frame_h), _p(scratch)))
+
+
 def det_expf(x: float) -> float:
     return float(lib().oracle_det_expf(C.c_float(x)))
 

@@ -335,3 +335,78 @@ int oracle_door_state(const uint8_t* rgb, uint32_t w, uint32_t h, uint32_t strid
     float density = (float)count / (float)(bw * bh);
     return (double)density > 0.1 ? 1 : 0;
 }
+
+/* ---- depth post-processing --------------------------- */
+
+/* src/vision/tk_depth_midas.c:473-499 (convert_inverse_depth_to_metric),
+ * statement for statement: extrema seeded with data[0] and updated with strict
+ * compares (a NaN never replaces them; a NaN seed sticks), `max - min < 1e-6f`
+ * -> every element = max_depth, else max_depth - (d-min)/(max-min)*(max_depth-min_depth).
+ * Built with -ffp-contract=off: one rounding per operation.  PARITY UNPINNED BY
+ * EXECUTION — the reference file cannot compile here (ONNX Runtime C++ API inside
+ * a .c file) and no reference test pins it; the restatement is the code above
+ * re-typed. */
+void oracle_inverse_depth_to_metric(const float* in, float* out, size_t n, float min_depth, float max_depth) {
+    if (n == 0) return;
+    float min_val = in[0], max_val = in[0];
+    for (size_t i = 1; i < n; i++) {
+        if (in[i] < min_val) min_val = in[i];
+        if (in[i] > max_val) max_val = in[i];
+    }
+    if (max_val - min_val < 1e-6f) {
+        for (size_t i = 0; i < n; i++) out[i] = max_depth;
+        return;
+    }
+    for (size_t i = 0; i < n; i++) {
+        float normalized = (in[i] - min_val) / (max_val - min_val);
+        out[i] = max_depth - normalized * (max_depth - min_depth);
+    }
+}
+
+/* Rust `f32 as u32`: saturating, NaN -> 0. */
+static uint32_t rust_f32_as_u32(float f) {
+    if (!(f > 0.0f)) return 0;                /* negatives, -0, NaN */
+    if (f >= 4294967296.0f) return 0xffffffffu;
+    return (uint32_t)f;
+}
+static int cmp_f32(const void* a, const void* b) {
+    float x = *(const float*)a, y = *(const float*)b;
+    return (x > y) - (x < y);
+}
+/* src/vision/src/object_analysis.rs:227-279 (calculate_raw_distance): bbox ->
+ * normalised corners (f32 divide) -> depth-map pixel via `.round() as u32`
+ * (half away from zero, saturating) -> inclusive window -> samples with
+ * 0.1 < d < 100 -> if >= 10: sort, q1 = v[len/4], q3 = v[len*3/4], fence
+ * q1 - 1.5 iqr .. q3 + 1.5 iqr, mean of the samples inside as a sequential f32
+ * sum in ascending order / count; otherwise -1.  i32 `x + w` wraps (release
+ * build).  `scratch` must hold depth_w*depth_h floats.
+ * Pinned by the reference's own unit test (object_analysis.rs:286-347): a
+ * 20x20 box over a 100x100 map of 10.0 -> 10.0, of 12.0 -> 12.0 (the Kalman
+ * smoothing that follows is downstream, out of scope). */
+float oracle_detection_distance(int bx, int by, int bw, int bh, const float* depth, uint32_t depth_w,
+                                uint32_t depth_h, uint32_t frame_w, uint32_t frame_h, float* scratch) {
+    float fw = (float)frame_w, fh = (float)frame_h;
+    int xr = (int)((uint32_t)bx + (uint32_t)bw), yb = (int)((uint32_t)by + (uint32_t)bh);
+    float nx0 = (float)bx / fw, ny0 = (float)by / fh, nx1 = (float)xr / fw, ny1 = (float)yb / fh;
+    uint32_t x0 = rust_f32_as_u32(roundf(nx0 * (float)(depth_w - 1)));
+    uint32_t y0 = rust_f32_as_u32(roundf(ny0 * (float)(depth_h - 1)));
+    uint32_t x1 = rust_f32_as_u32(roundf(nx1 * (float)(depth_w - 1)));
+    uint32_t y1 = rust_f32_as_u32(roundf(ny1 * (float)(depth_h - 1)));
+    if (x0 >= depth_w || y0 >= depth_h || x1 >= depth_w || y1 >= depth_h || x0 >= x1 || y0 >= y1) return -1.0f;
+    size_t n = 0;
+    for (uint32_t y = y0; y <= y1; ++y)
+        for (uint32_t x = x0; x <= x1; ++x) {
+            float d = depth[(size_t)y * depth_w + x];
+            if (d > 0.1f && d < 100.0f) scratch[n++] = d;
+        }
+    if (n < 10) return -1.0f;
+    qsort(scratch, n, sizeof(float), cmp_f32);
+    float q1 = scratch[n / 4], q3 = scratch[n * 3 / 4];
+    float iqr = q3 - q1;
+    float lower = q1 - 1.5f * iqr, upper = q3 + 1.5f * iqr;
+    float sum = 0.0f;
+    size_t cnt = 0;
+    for (size_t i = 0; i < n; ++i)
+        if (scratch[i] >= lower && scratch[i] <= upper) { sum += scratch[i]; cnt++; }
+    return cnt ? sum / (float)cnt : -1.0f;
+}

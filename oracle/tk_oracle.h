@@ -85,6 +85,12 @@ int oracle_dominant_color(const uint8_t* rgb, uint32_t w, uint32_t h, uint32_t s
 int oracle_door_state(const uint8_t* rgb, uint32_t w, uint32_t h, uint32_t stride,
                       int bx, int by, int bw, int bh, int32_t* edge_pixels);
 
+/* (f1) MiDaS inverse depth -> metric, src/vision/tk_depth_midas.c:473-499 (unpinned by execution). */
+void oracle_inverse_depth_to_metric(const float* in, float* out, size_t n, float min_depth, float max_depth);
+/* (f2) per-detection distance, src/vision/src/object_analysis.rs:227-279; scratch: depth_w*depth_h floats. */
+float oracle_detection_distance(int bx, int by, int bw, int bh, const float* depth, uint32_t depth_w,
+                                uint32_t depth_h, uint32_t frame_w, uint32_t frame_h, float* scratch);
+
 float oracle_det_expf(float x);
 float oracle_det_sigmoidf(float x);
 

@@ -61,6 +61,7 @@ def test_headers_are_plain_c_and_layouts_match(tmp_path):
         "tk_b200_color_params_t": capi.ColorParams, "tk_b200_door_params_t": capi.DoorParams,
         "tk_tensor_descriptor_t": capi.TensorDescriptor, "tk_cuda_dispatcher_config_t": capi.DispatcherConfig,
         "tk_b200_pipeline_config_t": capi.PipelineConfig,
+        "tk_b200_depth_metric_params_t": capi.DepthMetricParams, "tk_b200_distance_params_t": capi.DistanceParams,
     }
     body = "\n".join(f'    printf("{n} %zu\\n", sizeof({n}));' for n in structs)
     prog.write_text('#include <stdio.h>\n#include "tk_b200_vision.h"\nint main(void) {\n' + body +

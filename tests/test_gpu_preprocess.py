@@ -120,6 +120,23 @@ def test_rgba8():
     assert np.array_equal(bits(got), bits(O.preprocess_rgb8(fr, 96, 96)))
 
 
+@pytest.mark.parametrize("w,h,ow,oh", [(1920, 1080, 640, 640), (321, 203, 96, 80)])
+def test_bgr8_ffi_container_rows(w, h, ow, oh):
+    """TK_VISION_FMT_BGR24 with rows aligned up to TK_SIMD_ALIGNMENT = 32 bytes
+    (src/ffi/c_api/tk_ffi_api.c:878-892): tensor planes stay R, G, B, so the result is the
+    reference pre-processor's on the channel-reversed frame, bit for bit."""
+    fr = synth.rgb_frame(w, h, 9)
+    stride = (3 * w + 31) // 32 * 32
+    buf = np.full((h, stride), 0xAB, np.uint8)
+    buf[:, :3 * w] = fr[:, :, ::-1].reshape(h, 3 * w)
+    ref = O.preprocess_rgb8(fr, ow, oh)
+    got = run(buf.reshape(1, -1), ow, oh, width=w, height=h, fmt=V.PIXEL_BGR8, stride=stride)[0]
+    assert np.array_equal(bits(got), bits(ref))
+    got16 = run(buf.reshape(1, -1), ow, oh, width=w, height=h, fmt=V.PIXEL_BGR8, stride=stride,
+                out_dtype=torch.float16, arith=V.ARITH_HALF)[0].astype(np.float32)
+    assert np.all(np.abs(got16 - ref) <= 1e-2 + 1e-2 * np.abs(ref))
+
+
 @pytest.mark.parametrize("w,h", [(3840, 2160), (640, 480), (130, 66)])
 def test_i420(w, h):
     buf = synth.i420_frame(w, h, 8)

@@ -215,3 +215,51 @@ def test_i420_grey_is_identity():
     buf[: w * h] = np.arange(w * h) % 256
     rgb = O.i420_to_rgb8(buf, w, h)
     assert np.array_equal(rgb[..., 0].reshape(-1), buf[: w * h]) and np.array_equal(rgb[..., 0], rgb[..., 2])
+
+
+def test_inverse_depth_to_metric_properties():
+    """src/vision/tk_depth_midas.c:473-499: min -> max_depth, max -> min_depth, monotone decreasing; flat -> max_depth."""
+    rng = np.random.default_rng(0)
+    a = rng.random((64, 64), dtype=np.float32) * 1000
+    m = O.inverse_depth_to_metric(a)
+    assert m[np.unravel_index(a.argmin(), a.shape)] == np.float32(10.0)
+    assert abs(m[np.unravel_index(a.argmax(), a.shape)] - np.float32(0.1)) < 1e-6
+    o = np.argsort(a.reshape(-1))
+    assert np.all(np.diff(m.reshape(-1)[o]) <= 0)
+    assert np.all(O.inverse_depth_to_metric(np.full((8, 8), 2.5, np.float32)) == np.float32(10.0))
+    # numpy restatement of the same expression, one rounding per operation
+    mn, mx = a.min(), a.max()
+    want = np.float32(10.0) - ((a - mn) / (mx - mn)) * (np.float32(10.0) - np.float32(0.1))
+    assert np.array_equal(m.view(np.uint32), want.astype(np.float32).view(np.uint32))
+
+
+def test_detection_distance_reference_kat():
+    """The reference's own unit test (src/vision/src/object_analysis.rs:286-347): the raw measurement for a 20x20
+    box over a constant 10.0 (then 12.0) region of a 100x100 map is that constant."""
+    d1 = np.zeros((100, 100), np.float32); d1[10:30, 10:30] = 10.0
+    d2 = np.zeros((100, 100), np.float32); d2[11:31, 11:31] = 12.0
+    assert O.detection_distance((10, 10, 20, 20), d1, 100, 100) == 10.0
+    assert O.detection_distance((11, 11, 20, 20), d2, 100, 100) == 12.0
+    # the window is inclusive and rounds through (w-1): 21x21 samples, 400 of them valid
+    assert O.detection_distance((10, 10, 20, 20), np.zeros((100, 100), np.float32), 100, 100) == -1.0
+    assert O.detection_distance((10, 10, 0, 20), d1, 100, 100) == -1.0          # x_min >= x_max
+    assert O.detection_distance((90, 90, 20, 20), d1, 100, 100) == -1.0          # beyond the map
+    # IQR fence drops the outliers: 300 samples of 5.0 and 20 of 90.0 -> 5.0
+    d3 = np.zeros((100, 100), np.float32); d3[0:16, 0:20] = 5.0; d3[0, 0:20] = 90.0
+    assert O.detection_distance((0, 0, 19, 15), d3, 100, 100) == 5.0
+    # python restatement on random data
+    rng = np.random.default_rng(3)
+    dm = rng.gamma(2.0, 3.0, (50, 60)).astype(np.float32)
+    x0, y0, x1, y1 = [int(np.floor(v + 0.5)) for v in (np.float32(8) / np.float32(120) * np.float32(59),
+                                                          np.float32(6) / np.float32(100) * np.float32(49),
+                                                          np.float32(8 + 70) / np.float32(120) * np.float32(59),
+                                                          np.float32(6 + 60) / np.float32(100) * np.float32(49))]
+    v = np.sort(dm[y0:y1 + 1, x0:x1 + 1].reshape(-1))
+    v = v[(v > np.float32(0.1)) & (v < np.float32(100))]
+    q1, q3 = v[len(v) // 4], v[len(v) * 3 // 4]
+    iqr = q3 - q1
+    f = v[(v >= q1 - np.float32(1.5) * iqr) & (v <= q3 + np.float32(1.5) * iqr)]
+    acc = np.float32(0)
+    for t in f:
+        acc = np.float32(acc + t)
+    assert O.detection_distance((8, 6, 70, 60), dm, 120, 100) == float(np.float32(acc / np.float32(len(f))))

@@ -15,9 +15,10 @@ LIB_PATH = os.path.join(PKG_DIR, "libtk_b200.so")
 TK_SUCCESS = 0
 TK_ERROR_INVALID_ARGUMENT = 1001
 TK_ERROR_NOT_IMPLEMENTED = 1003
+TK_ERROR_BUFFER_TOO_SMALL = 1004
 TK_ERROR_INVALID_DIMENSIONS = 5008
 
-PIXEL_RGB8, PIXEL_RGBA8, PIXEL_I420 = 0, 1, 2
+PIXEL_RGB8, PIXEL_RGBA8, PIXEL_I420, PIXEL_BGR8 = 0, 1, 2, 3
 OUT_F32, OUT_F16 = 0, 1
 RESIZE_STRETCH, RESIZE_LETTERBOX = 0, 1
 ARITH_EXACT, ARITH_FAST, ARITH_HALF = 0, 1, 2
@@ -115,6 +116,18 @@ class DoorParams(C.Structure):             # tk_b200_door_params_t
                 ("d_states", C.c_void_p), ("d_edge_pixels", C.c_void_p)]
 
 
+class DepthMetricParams(C.Structure):      # tk_b200_depth_metric_params_t
+    _fields_ = [("d_inverse_depth", C.c_void_p), ("d_metric_depth", C.c_void_p), ("num_maps", C.c_uint32),
+                ("width", C.c_uint32), ("height", C.c_uint32), ("min_depth", C.c_float), ("max_depth", C.c_float)]
+
+
+class DistanceParams(C.Structure):         # tk_b200_distance_params_t
+    _fields_ = [("d_detections", C.c_void_p), ("d_num_detections", C.c_void_p), ("num_frames", C.c_uint32),
+                ("max_detections", C.c_uint32), ("d_depth_maps", C.c_void_p), ("depth_width", C.c_uint32),
+                ("depth_height", C.c_uint32), ("frame_width", C.c_uint32), ("frame_height", C.c_uint32),
+                ("d_distances", C.c_void_p), ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t)]
+
+
 class TensorDescriptor(C.Structure):       # tk_tensor_descriptor_t
     _fields_ = [("buffer", C.c_void_p), ("type", C.c_int), ("layout", C.c_int), ("dimensions", C.c_uint32),
                 ("shape", C.c_uint32 * 8), ("stride", C.c_size_t * 8), ("data_size_bytes", C.c_size_t),
@@ -161,6 +174,8 @@ def lib() -> C.CDLL:
         _lib.tk_b200_dispatch_stream.restype = C.c_void_p
         _lib.tk_b200_dispatch_stream.argtypes = [C.c_void_p]
         _lib.tk_b200_dispatch_device.argtypes = [C.c_void_p]
+        _lib.tk_b200_detection_distance_workspace_bytes.restype = C.c_size_t
+        _lib.tk_b200_detection_distance_workspace_bytes.argtypes = [C.c_uint32, C.c_uint32]
         _lib.tk_b200_host_free.argtypes = [C.c_void_p]
         _lib.tk_b200_host_free.restype = None
     return _lib

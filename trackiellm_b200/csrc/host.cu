@@ -172,7 +172,7 @@ extern "C" tk_error_code_t tk_preprocessor_resize_and_normalize_to_chw(const tk_
     if (frame->width < 2 || frame->height < 2) return TK_ERROR_INVALID_ARGUMENT;
     uint32_t bpp; size_t in_bytes;
     switch (frame->format) {
-        case TK_PIXEL_FORMAT_RGB8: bpp = 3; break;
+        case TK_PIXEL_FORMAT_RGB8: case TK_PIXEL_FORMAT_BGR8: bpp = 3; break;
         case TK_PIXEL_FORMAT_RGBA8: bpp = 4; break;
         case TK_PIXEL_FORMAT_I420: bpp = 1; break;
         default: return TK_ERROR_INVALID_ARGUMENT;

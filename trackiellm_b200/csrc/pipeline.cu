@@ -57,7 +57,8 @@ struct tk_b200_pipeline_s {
 using namespace tkb;
 
 static size_t frame_bytes_of(const tk_b200_pipeline_config_t& c) {
-    uint32_t bpp = c.input_format == TK_PIXEL_FORMAT_RGB8 ? 3 : (c.input_format == TK_PIXEL_FORMAT_RGBA8 ? 4 : 1);
+    uint32_t bpp = (c.input_format == TK_PIXEL_FORMAT_RGB8 || c.input_format == TK_PIXEL_FORMAT_BGR8) ? 3
+                   : (c.input_format == TK_PIXEL_FORMAT_RGBA8 ? 4 : 1);
     size_t stride = c.input_stride_bytes ? c.input_stride_bytes : (size_t)c.input_width * bpp;
     size_t b = stride * c.input_height;
     if (c.input_format == TK_PIXEL_FORMAT_I420) b += 2 * (stride / 2) * (size_t)(c.input_height / 2);
@@ -105,7 +106,7 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     if (cfg->input_width < 2 || cfg->input_height < 2 || cfg->tensor_width == 0 || cfg->tensor_height == 0)
         return TK_ERROR_INVALID_DIMENSIONS;
     if (cfg->input_format != TK_PIXEL_FORMAT_RGB8 && cfg->input_format != TK_PIXEL_FORMAT_RGBA8 &&
-        cfg->input_format != TK_PIXEL_FORMAT_I420)
+        cfg->input_format != TK_PIXEL_FORMAT_I420 && cfg->input_format != TK_PIXEL_FORMAT_BGR8)
         return TK_ERROR_INVALID_ARGUMENT;
     if (cfg->max_candidates > 4096) return TK_ERROR_INVALID_ARGUMENT;
     int count = 0;

@@ -54,6 +54,7 @@ struct PreK {
     uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty output rows in flight
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
+    uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
 };
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
@@ -408,7 +409,7 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
                     const uint2 vs[3] = {vr, vg, vb};
 #pragma unroll
                     for (int c = 0; c < 3; ++c) {
-                        const size_t e = ((size_t)f * 3 + c) * plane + pix;
+                        const size_t e = ((size_t)f * 3 + (p.swap_rb ? 2 - c : c)) * plane + pix;
                         if (p.vec_store) {
                             __stcs(reinterpret_cast<uint2*>(outp + e), vs[c]);
                         } else {
@@ -447,7 +448,7 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
                 const size_t pix = (size_t)h * p.dst_w + 4u * q;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const size_t e = ((size_t)f * 3 + c) * plane + pix;
+                    const size_t e = ((size_t)f * 3 + (p.swap_rb ? 2 - c : c)) * plane + pix;
                     if (p.vec_store) {
                         if constexpr (F16) {
                             __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
@@ -562,8 +563,10 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
         case TK_PIXEL_FORMAT_RGB8:  fmt = FMT_RGB8;  bpp = 3; break;
         case TK_PIXEL_FORMAT_RGBA8: fmt = FMT_RGBA8; bpp = 4; break;
         case TK_PIXEL_FORMAT_I420:  fmt = FMT_I420;  bpp = 1; break;
+        case TK_PIXEL_FORMAT_BGR8:  fmt = FMT_RGB8;  bpp = 3; break;   // same gather, planes swapped on store
         default: return TK_ERROR_INVALID_ARGUMENT;
     }
+    const bool bgr = prm->input_format == TK_PIXEL_FORMAT_BGR8;
     const DeviceInfo* dev = device_info();
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
 
@@ -583,8 +586,11 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     // src/vision/tk_image_preprocessor.c:43-44 (uint -> float, fp32 divide)
     k.x_ratio = ((float)k.src_w - 1.0f) / (float)k.new_w;
     k.y_ratio = ((float)k.src_h - 1.0f) / (float)k.new_h;
+    k.swap_rb = bgr ? 1u : 0u;
     for (int c = 0; c < 3; ++c) {
-        float mu = (&prm->mean.x)[c], sd = (&prm->std_dev.x)[c];
+        // constants are indexed by SOURCE channel; BGR byte c is tensor channel 2 - c
+        const int tc = bgr ? 2 - c : c;
+        float mu = (&prm->mean.x)[tc], sd = (&prm->std_dev.x)[tc];
         k.mean[c] = mu; k.stdv[c] = sd; k.rstd[c] = rn_reciprocal(sd);
         k.fscale[c] = (float)(1.0 / (255.0 * (double)sd));
         k.fbias[c] = (float)(-(double)mu / (double)sd);

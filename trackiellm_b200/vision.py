@@ -15,7 +15,7 @@ import torch
 
 from . import _capi as capi
 from ._capi import (ACT_RAW, ACT_SIGMOID, ACT_SOFTMAX, ARITH_EXACT, ARITH_FAST, ARITH_HALF, OUT_F16, OUT_F32,
-                    PIXEL_I420, PIXEL_RGB8, PIXEL_RGBA8, RESIZE_LETTERBOX, RESIZE_STRETCH)
+                    PIXEL_BGR8, PIXEL_I420, PIXEL_RGB8, PIXEL_RGBA8, RESIZE_LETTERBOX, RESIZE_STRETCH)
 
 IMAGENET_MEAN = (0.485, 0.456, 0.406)   # src/vision/tk_object_detector.c:248
 IMAGENET_STD = (0.229, 0.224, 0.225)    # src/vision/tk_object_detector.c:249
@@ -248,6 +248,43 @@ def kernels_depth_to_point_cloud(depth: torch.Tensor, fx: float, fy: float, cx: 
     p = capi.DepthPointsParams(depth.data_ptr(), w, h, out.data_ptr(), fx, fy, cx, cy)
     with torch.cuda.device(depth.device):
         capi.check(capi.lib().tk_kernels_depth_to_point_cloud(C.byref(p), _stream()), "tk_kernels_depth_to_point_cloud")
+    return out
+
+
+def inverse_depth_to_metric(inv: torch.Tensor, min_depth: float = 0.1, max_depth: float = 10.0,
+                            out: torch.Tensor | None = None) -> torch.Tensor:
+    """tk_kernels_inverse_depth_to_metric: [N,H,W] (or [H,W]) MiDaS inverse depth -> metric depth, each map
+    normalised by its own min/max (src/vision/tk_depth_midas.c:473-499, defaults :46-47)."""
+    _require_cuda(inv, "inv")
+    n = 1 if inv.dim() == 2 else inv.shape[0]
+    h, w = inv.shape[-2:]
+    if out is None:
+        out = torch.empty_like(inv)
+    p = capi.DepthMetricParams(inv.data_ptr(), out.data_ptr(), n, w, h, min_depth, max_depth)
+    with torch.cuda.device(inv.device):
+        capi.check(capi.lib().tk_kernels_inverse_depth_to_metric(C.byref(p), _stream()), "tk_kernels_inverse_depth_to_metric")
+    return out
+
+
+def detection_distance(dets: torch.Tensor, counts: torch.Tensor | None, depth: torch.Tensor, frame_w: int,
+                       frame_h: int) -> torch.Tensor:
+    """tk_kernels_detection_distance: dets [N,max_det,7] i32 view of tk_b200_candidate_t, counts [N] (or None),
+    depth [N,H,W] f32 -> [N,max_det] f32 distances, -1 where there is no estimate
+    (src/vision/src/object_analysis.rs:227-279)."""
+    _require_cuda(dets, "dets")
+    _require_cuda(depth, "depth")
+    n, max_det = dets.shape[0], dets.shape[1]
+    h, w = depth.shape[-2:]
+    out = torch.empty((n, max_det), dtype=torch.float32, device=dets.device)
+    need = int(capi.lib().tk_b200_detection_distance_workspace_bytes(w, h))
+    ws = torch.empty((need,), dtype=torch.uint8, device=dets.device) if need else None
+    p = capi.DistanceParams(dets.data_ptr(), counts.data_ptr() if counts is not None else None, n, max_det,
+                            depth.data_ptr(), w, h, frame_w, frame_h, out.data_ptr(),
+                            ws.data_ptr() if ws is not None else None, need)
+    with torch.cuda.device(dets.device):
+        capi.check(capi.lib().tk_kernels_detection_distance(C.byref(p), _stream()), "tk_kernels_detection_distance")
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream())
     return out
 
 
