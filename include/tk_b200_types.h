@@ -145,6 +145,29 @@ typedef struct {
     tk_rect_t   bbox;
 } tk_detection_result_t;
 
+/* ---- src/vision/tk_vision_pipeline.h:56-61 -------------------------------- */
+typedef enum {
+    TK_VISION_BACKEND_CPU,
+    TK_VISION_BACKEND_CUDA,
+    TK_VISION_BACKEND_METAL,
+    TK_VISION_BACKEND_ROCM
+} tk_vision_backend_e;
+
+/* ---- src/vision/tk_object_detector.h:35-58 -------------------------------- */
+typedef struct tk_path_s tk_path_t;                       /* src/internal_tools/tk_file_manager.h:40 (opaque) */
+typedef struct tk_object_detector_s tk_object_detector_t;
+typedef struct {
+    tk_vision_backend_e backend;
+    int                 gpu_device_id;
+    tk_path_t*          model_path;
+    uint32_t            input_width;
+    uint32_t            input_height;
+    const char**        class_labels;   /* not copied; must outlive the detector */
+    size_t              class_count;
+    float               confidence_threshold;
+    float               iou_threshold;
+} tk_object_detector_config_t;
+
 /* ---- src/gpu/tk_gpu_helper.h:25-27,42-57,67-80,91-105,119-130 ------------- */
 typedef struct {
     float x, y, z;

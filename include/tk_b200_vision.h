@@ -75,8 +75,24 @@ TK_NODISCARD tk_error_code_t tk_cuda_tensor_nms(
 TK_NODISCARD tk_error_code_t tk_classify_dominant_color(const tk_video_frame_t* frame, const tk_rect_t* bbox, char** out_color_name);
 TK_NODISCARD tk_error_code_t tk_classify_door_state(const tk_video_frame_t* frame, const tk_rect_t* bbox, char** out_state_name);
 
-/* src/vision/tk_object_detector.h:157 */
+/* src/vision/tk_object_detector.h:96,102,138-143,157,166.  Same signatures and
+ * error behaviour.  The reference's create() opens an ONNX Runtime session on
+ * config->model_path (src/vision/tk_object_detector.c:93-120); ONNX Runtime is a
+ * third-party engine outside this path, so here the network is BOUND to the
+ * detector with tk_b200_object_detector_bind_inference (Part 2) and receives
+ * DEVICE pointers — the I/O-binding form of the reference's host-tensor call
+ * (:266-294) — so pre-process -> network -> post-process never leaves HBM.
+ * backend must be TK_VISION_BACKEND_CUDA (no CPU fallback: TK_ERROR_NOT_IMPLEMENTED).
+ * detect(): upload, fused pre-process (fp32, ImageNet mean/std of :248-249),
+ * bound network, decode + class-wise NMS, boxes restored to frame px, results
+ * malloc'd for tk_object_detector_free_results.  Not thread-safe per detector
+ * (tk_object_detector.h:134-137). */
+TK_NODISCARD tk_error_code_t tk_object_detector_create(tk_object_detector_t** out_detector, const tk_object_detector_config_t* config);
+void tk_object_detector_destroy(tk_object_detector_t** detector);
+TK_NODISCARD tk_error_code_t tk_object_detector_detect(tk_object_detector_t* detector, const tk_video_frame_t* video_frame,
+                                                       tk_detection_result_t** out_results, size_t* out_result_count);
 void tk_object_detector_free_results(tk_detection_result_t** results);
+void tk_object_detector_update_thresholds(tk_object_detector_t* detector, float confidence_threshold, float iou_threshold);
 
 /* ======================================================================== */
 /* Part 2 — additive entry points                                            */
@@ -328,6 +344,26 @@ TK_NODISCARD tk_error_code_t tk_b200_postprocess_detections(
     const char* const* class_labels, size_t class_count,
     uint32_t frame_width, uint32_t frame_height, uint32_t input_width, uint32_t input_height,
     tk_detection_result_t** out_results, size_t* out_result_count);
+
+/* The detector network behind tk_object_detector_detect, as a device-side hook
+ * (the reference copies the tensor to the host around
+ * OrtRun, src/vision/tk_object_detector.c:266-269,286-294).  Called on the
+ * detector's device with
+ *   d_input  f32 [num_frames][3][input_height][input_width]  (ready on `stream`)
+ *   d_output f32 [num_frames][num_proposals][5 + class_count] (to be written on `stream`)
+ * and must only ENQUEUE work on `stream`.  A non-zero return aborts detect()
+ * with TK_ERROR_INFERENCE_FAILED. */
+typedef tk_error_code_t (*tk_b200_inference_fn)(void* user, const float* d_input, uint32_t num_frames,
+                                                uint32_t input_width, uint32_t input_height, float* d_output,
+                                                uint32_t num_proposals, uint32_t row_length, cudaStream_t stream);
+TK_NODISCARD tk_error_code_t tk_b200_object_detector_bind_inference(
+    tk_object_detector_t* detector, tk_b200_inference_fn fn, void* user, uint32_t num_proposals,
+    tk_b200_activation_e activation);
+/* Batched detect: num_frames frames of ONE geometry and format; out_results[i]
+ * is malloc'd per frame (free each with tk_object_detector_free_results). */
+TK_NODISCARD tk_error_code_t tk_b200_object_detector_detect_batch(
+    tk_object_detector_t* detector, const tk_video_frame_t* frames, uint32_t num_frames,
+    tk_detection_result_t** out_results, size_t* out_result_counts);
 
 /* Handle accessors, so tk_kernels_* launchers can run on a dispatcher's buffers
  * and compute stream. */

@@ -19,7 +19,7 @@ def declared_functions():
     for hdr in ("tk_b200_vision.h", "tk_b200_types.h"):
         src = open(os.path.join(INC, hdr)).read()
         src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-        for m in re.finditer(r"\b(tk_[a-z0-9_]+)\s*\(", src):
+        for m in re.finditer(r"\b(tk_[a-z0-9_]+)\s*\((?!\s*\*)", src):   # (?!..): not a function-pointer typedef
             names.add(m.group(1))
     return sorted(names)
 
@@ -40,6 +40,8 @@ def test_reference_entry_points_present():
               "tk_cuda_dispatch_upload_async", "tk_cuda_dispatch_download_async", "tk_cuda_dispatch_synchronize",
               "tk_cuda_dispatch_preprocess_image", "tk_cuda_dispatch_depth_to_point_cloud", "tk_cuda_tensor_nms",
               "tk_classify_dominant_color", "tk_classify_door_state", "tk_object_detector_free_results",
+              "tk_object_detector_create", "tk_object_detector_destroy", "tk_object_detector_detect",
+              "tk_object_detector_update_thresholds",
               "tk_error_to_string", "tk_error_set_detail", "tk_error_get_detail"):
         assert hasattr(lib, n), n
 
@@ -61,6 +63,7 @@ def test_headers_are_plain_c_and_layouts_match(tmp_path):
         "tk_b200_color_params_t": capi.ColorParams, "tk_b200_door_params_t": capi.DoorParams,
         "tk_tensor_descriptor_t": capi.TensorDescriptor, "tk_cuda_dispatcher_config_t": capi.DispatcherConfig,
         "tk_b200_pipeline_config_t": capi.PipelineConfig,
+        "tk_object_detector_config_t": capi.ObjectDetectorConfig,
         "tk_b200_depth_metric_params_t": capi.DepthMetricParams, "tk_b200_distance_params_t": capi.DistanceParams,
     }
     body = "\n".join(f'    printf("{n} %zu\\n", sizeof({n}));' for n in structs)

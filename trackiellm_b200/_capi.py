@@ -128,6 +128,18 @@ class DistanceParams(C.Structure):         # tk_b200_distance_params_t
                 ("d_distances", C.c_void_p), ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t)]
 
 
+class ObjectDetectorConfig(C.Structure):   # tk_object_detector_config_t (src/vision/tk_object_detector.h:42-58)
+    _fields_ = [("backend", C.c_int), ("gpu_device_id", C.c_int), ("model_path", C.c_void_p),
+                ("input_width", C.c_uint32), ("input_height", C.c_uint32), ("class_labels", C.POINTER(C.c_char_p)),
+                ("class_count", C.c_size_t), ("confidence_threshold", C.c_float), ("iou_threshold", C.c_float)]
+
+
+# tk_b200_inference_fn
+INFERENCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
+                           C.c_uint32, C.c_uint32, C.c_void_p)
+VISION_BACKEND_CPU, VISION_BACKEND_CUDA, VISION_BACKEND_METAL, VISION_BACKEND_ROCM = 0, 1, 2, 3
+
+
 class TensorDescriptor(C.Structure):       # tk_tensor_descriptor_t
     _fields_ = [("buffer", C.c_void_p), ("type", C.c_int), ("layout", C.c_int), ("dimensions", C.c_uint32),
                 ("shape", C.c_uint32 * 8), ("stride", C.c_size_t * 8), ("data_size_bytes", C.c_size_t),
@@ -176,6 +188,9 @@ def lib() -> C.CDLL:
         _lib.tk_b200_dispatch_device.argtypes = [C.c_void_p]
         _lib.tk_b200_detection_distance_workspace_bytes.restype = C.c_size_t
         _lib.tk_b200_detection_distance_workspace_bytes.argtypes = [C.c_uint32, C.c_uint32]
+        _lib.tk_object_detector_update_thresholds.restype = None
+        _lib.tk_object_detector_update_thresholds.argtypes = [C.c_void_p, C.c_float, C.c_float]
+        _lib.tk_object_detector_destroy.restype = None
         _lib.tk_b200_host_free.argtypes = [C.c_void_p]
         _lib.tk_b200_host_free.restype = None
     return _lib

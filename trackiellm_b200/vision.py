@@ -444,6 +444,87 @@ class Pipeline:
                    "tk_b200_pipeline_process_host")
 
 
+class ObjectDetector:
+    """tk_object_detector_create / _detect / _update_thresholds / _destroy (src/vision/tk_object_detector.h:96-166)
+    with the detector network bound as a device-side hook: `network(d_input_ptr, n, in_w, in_h, d_output_ptr,
+    num_proposals, row_len, stream_ptr) -> int` enqueues the head tensor on the stream (0 = success)."""
+
+    def __init__(self, *, device_id: int = 0, input_w: int = 640, input_h: int = 640, class_labels=None,
+                 num_classes: int | None = None, conf_thr: float = 0.5, iou_thr: float = 0.5,
+                 backend: int = capi.VISION_BACKEND_CUDA, model_path: bytes = b"model.onnx"):
+        self._labels = None
+        nlab = num_classes if num_classes is not None else (len(class_labels) if class_labels else 0)
+        if class_labels:
+            self._labels = (C.c_char_p * len(class_labels))(*[s.encode() for s in class_labels])
+        self._path = C.create_string_buffer(model_path)       # opaque tk_path_t*: never dereferenced by the library
+        cfg = capi.ObjectDetectorConfig(backend, device_id, C.cast(self._path, C.c_void_p), input_w, input_h,
+                                        C.cast(self._labels, C.POINTER(C.c_char_p)) if self._labels else None,
+                                        nlab, conf_thr, iou_thr)
+        self._h = C.c_void_p()
+        self._cb = None
+        capi.check(capi.lib().tk_object_detector_create(C.byref(self._h), C.byref(cfg)), "tk_object_detector_create")
+
+    def bind_network(self, network, num_proposals: int, act: int = ACT_RAW) -> None:
+        def tramp(user, d_in, n, w, h, d_out, p, l, stream):
+            try:
+                return int(network(d_in, n, w, h, d_out, p, l, stream) or 0)
+            except Exception:      # never unwind through C
+                import traceback
+                traceback.print_exc()
+                return 1
+        self._cb = capi.INFERENCE_FN(tramp)
+        capi.check(capi.lib().tk_b200_object_detector_bind_inference(self._h, self._cb, None, C.c_uint32(num_proposals),
+                                                                     C.c_int(act)), "tk_b200_object_detector_bind_inference")
+
+    def update_thresholds(self, conf_thr: float, iou_thr: float) -> None:
+        capi.lib().tk_object_detector_update_thresholds(self._h, conf_thr, iou_thr)
+
+    @staticmethod
+    def _records(res, cnt):
+        return [(int(res[i].class_id), res[i].label.decode() if res[i].label else None, float(res[i].confidence),
+                 (res[i].bbox.x, res[i].bbox.y, res[i].bbox.w, res[i].bbox.h)) for i in range(cnt)]
+
+    def detect(self, frame: np.ndarray, fmt: int = PIXEL_RGB8, width: int | None = None, height: int | None = None,
+               stride: int = 0):
+        """tk_object_detector_detect on one HOST frame -> [(class_id, label, confidence, (x, y, w, h)), ...]."""
+        frame = np.ascontiguousarray(frame, np.uint8)
+        h, w = (height, width) if width else frame.shape[:2]
+        vf = capi.VideoFrame(w, h, stride, fmt, frame.ctypes.data)
+        res = C.POINTER(capi.DetectionResult)()
+        cnt = C.c_size_t(0)
+        capi.check(capi.lib().tk_object_detector_detect(self._h, C.byref(vf), C.byref(res), C.byref(cnt)),
+                   "tk_object_detector_detect")
+        out = self._records(res, cnt.value)
+        capi.lib().tk_object_detector_free_results(C.byref(res))
+        return out
+
+    def detect_batch(self, frames: np.ndarray, fmt: int = PIXEL_RGB8):
+        """tk_b200_object_detector_detect_batch on HOST frames [N,H,W,3|4]."""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape[:3]
+        vfs = (capi.VideoFrame * n)(*[capi.VideoFrame(w, h, 0, fmt, frames[i].ctypes.data) for i in range(n)])
+        res = (C.POINTER(capi.DetectionResult) * n)()
+        cnt = (C.c_size_t * n)()
+        capi.check(capi.lib().tk_b200_object_detector_detect_batch(self._h, vfs, C.c_uint32(n), res, cnt),
+                   "tk_b200_object_detector_detect_batch")
+        out = []
+        for i in range(n):
+            out.append(self._records(res[i], cnt[i]))
+            p = res[i]
+            capi.lib().tk_object_detector_free_results(C.byref(p))
+        return out
+
+    def close(self) -> None:
+        if self._h:
+            capi.lib().tk_object_detector_destroy(C.byref(self._h))
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
 def postprocess_detections(logits: np.ndarray, *, act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5,
                            max_detections: int = 500, class_labels: list[str] | None = None,
                            frame_wh=(0, 0), input_wh=(0, 0)):
