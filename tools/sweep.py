@@ -60,6 +60,50 @@ def batch_sweep():
         torch.cuda.empty_cache()
 
 
+def other_kernels():
+    """HBM-bound secondary kernels: algorithmic bytes = every input byte once + every
+    output byte once; buffers of >= 256 MB per launch so every iteration streams from HBM."""
+    print("\n| kernel | workload | us/launch | algorithmic GB/s | % of 6538 |")
+    print("|---|---|---|---|---|")
+    rows = []
+    n, h, w = 1024, 256, 256                                   # 1024 MiDaS maps of 256x256: 268 MB in, 268 MB out
+    inv = torch.rand((n, h, w), device="cuda") * 900 + 3
+    out = torch.empty_like(inv)
+    us = time_us(lambda: V.inverse_depth_to_metric(inv, out=out), 30)
+    rows.append(("inverse_depth_metric_kernel", f"{n} maps {h}x{w} f32 (min/max + convert, 8 B/element)", us, 8 * inv.numel()))
+    n2, h2, w2 = 256, 480, 640
+    inv2 = torch.rand((n2, h2, w2), device="cuda") * 900 + 3
+    out2 = torch.empty_like(inv2)
+    us = time_us(lambda: V.inverse_depth_to_metric(inv2, out=out2), 30)
+    rows.append(("inverse_depth_metric_kernel", f"{n2} maps {h2}x{w2} f32", us, 8 * inv2.numel()))
+    big = inv.view(n * h, w)                                    # one 262144 x 256 map for the single-map reference launchers
+    us = time_us(lambda: V.kernels_postprocess_depth_map(big, 0.37, 1.5), 30)
+    rows.append(("depth_scale_kernel", "67 M elements f32 (8 B/element)", us, 8 * big.numel()))
+    us = time_us(lambda: V.kernels_depth_to_point_cloud(big, 300.0, 310.0, 128.0, 128.0), 30)
+    rows.append(("depth_points_kernel", "67 M elements f32 -> xyz (16 B/element)", us, 16 * big.numel()))
+    x = torch.randn((4 * 1024 * 1024, 80), device="cuda")
+    us = time_us(lambda: V.kernels_softmax(x), 20)
+    rows.append(("softmax_tile_kernel", "4 M rows x 80 f32 (8 B/element)", us, 8 * x.numel()))
+    for name, wl, us, alg in rows:
+        print(f"| {name} | {wl} | {us:.1f} | {alg / us / 1e3:.0f} | {alg / us / 1e3 / PEAK * 100:.1f} |")
+    # latency-bound: per-detection distance over the pipeline's output shape
+    nf, md = 64, 500
+    depth = torch.rand((nf, 256, 256), device="cuda") * 20 + 0.2
+    rng = np.random.default_rng(0)
+    d = np.zeros((nf, md), V.CAND_DTYPE)
+    d["x"] = rng.integers(0, 500, (nf, md)); d["y"] = rng.integers(0, 500, (nf, md))
+    d["w"] = rng.integers(16, 320, (nf, md)); d["h"] = rng.integers(16, 320, (nf, md))
+    dets = torch.from_numpy(d.view(np.int32).reshape(nf, md, 7)).cuda()
+    cnt = torch.full((nf,), 56, dtype=torch.int32, device="cuda")
+    us = time_us(lambda: V.detection_distance(dets, cnt, depth, 640, 640), 20)
+    print(f"\ndetection_distance_kernel: {nf} frames x 56 detections (boxes 16..320 px of 640, depth maps 256x256): "
+          f"{us:.1f} us/launch = {nf * 56 / us:.2f} detections/us (latency-bound, shared-memory sort)")
+
+
 if __name__ == "__main__":
-    pre_geometry()
-    batch_sweep()
+    if len(sys.argv) > 1 and sys.argv[1] == "others":
+        other_kernels()
+    else:
+        pre_geometry()
+        batch_sweep()
+        other_kernels()
