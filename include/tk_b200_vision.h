@@ -239,7 +239,7 @@ TK_NODISCARD tk_error_code_t tk_kernels_inverse_depth_to_metric(const tk_b200_de
 typedef struct {
     const tk_b200_candidate_t* d_detections;     /* [N][max_detections] (bbox in frame px)   */
     const uint32_t*            d_num_detections; /* [N] or NULL = max_detections everywhere  */
-    uint32_t                   num_frames;       /* N <= 65535                               */
+    uint32_t                   num_frames;       /* N                                        */
     uint32_t                   max_detections;
     const float*               d_depth_maps;     /* [N][depth_height][depth_width]           */
     uint32_t                   depth_width, depth_height;

@@ -177,7 +177,8 @@ extern "C" tk_error_code_t tk_kernels_inverse_depth_to_metric(const tk_b200_dept
 // ------------------------------------------------------------------------- //
 namespace tkb {
 
-constexpr int kDistThreads = 256;
+constexpr int kDistThreads = 512;
+constexpr uint32_t kDistFrames = 1024;     // frames per launch (their count prefix lives in shared memory)
 constexpr uint32_t kDistChunk = 16384;     // samples sorted in shared memory at once (64 KB)
 constexpr uint32_t kDistSlots = 16;        // global scratch slots for windows with more samples
 constexpr uint32_t kDistMinPoints = 10;    // MIN_DEPTH_POINTS_FOR_STATS, object_analysis.rs:233
@@ -191,6 +192,7 @@ struct DistK {
     float* scratch;         // kDistSlots x depth_w*depth_h floats (or NULL)
     uint32_t num_frames, max_det, depth_w, depth_h, frame_w, frame_h;
     uint32_t smem_floats;   // capacity of the shared-memory sample buffer
+    uint32_t* ticket;       // work counter of this launch (zeroed before it)
 };
 
 __device__ __forceinline__ void cmp_swap(float* a, uint32_t lo, uint32_t hi) {
@@ -229,15 +231,125 @@ __device__ void sort_shared(float* s, uint32_t m, uint32_t lmax, uint32_t tid) {
     }
 }
 
-__global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const DistK k) {
-    extern __shared__ __align__(16) float sbuf[];
+// ---- register-resident sort of up to 512 * E samples ------------------------------------------
+// Thread t owns the E consecutive elements t*E .. t*E+E-1 (+inf beyond n).  Normalised bitonic
+// network: strides below E are compile-time min/max pairs in registers (2 instructions per
+// compare-exchange), thread strides 1..16 are warp shuffles, 32..256 go through shared memory.
+template <int E>
+__device__ __forceinline__ void regs_flip(float (&v)[E], int kk) {          // blocks of kk <= E inside the thread
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        const int off = e & (kk - 1), pe = (e & ~(kk - 1)) + kk - 1 - off;
+        if (e < pe) { const float lo = fminf(v[e], v[pe]), hi = fmaxf(v[e], v[pe]); v[e] = lo; v[pe] = hi; }
+    }
+}
+template <int E>
+__device__ __forceinline__ void regs_half(float (&v)[E], int j) {           // stride j < E inside the thread
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        if ((e & j) == 0) { const float lo = fminf(v[e], v[e | j]), hi = fmaxf(v[e], v[e | j]); v[e] = lo; v[e | j] = hi; }
+    }
+}
+// Compare-exchange with thread tid ^ mask; `rev`: the partner's elements in reverse order (flip step).
+template <int E>
+__device__ __forceinline__ void regs_cross(float (&v)[E], uint32_t tid, uint32_t mask, bool rev, float* xbuf) {
+    float o[E];
+    if (mask < 32u) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            const float fwd = __shfl_xor_sync(0xffffffffu, v[e], mask);
+            const float bwd = __shfl_xor_sync(0xffffffffu, v[E - 1 - e], mask);
+            o[e] = rev ? bwd : fwd;
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < E; ++e) xbuf[e * kDistThreads + tid] = v[e];
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < E; ++e) o[e] = xbuf[(rev ? E - 1 - e : e) * kDistThreads + (tid ^ mask)];
+        __syncthreads();
+    }
+    const bool lower = tid < (tid ^ mask);
+#pragma unroll
+    for (int e = 0; e < E; ++e) v[e] = lower ? fminf(v[e], o[e]) : fmaxf(v[e], o[e]);
+}
+template <int E>
+__device__ void sort_regs(float* a, uint32_t n, uint32_t tid) {
+    float v[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) { const uint32_t g = tid * E + e; v[e] = g < n ? a[g] : __int_as_float(0x7f800000); }
+    __syncthreads();                                           // `a` doubles as the exchange buffer
+#pragma unroll
+    for (int kk = 2; kk <= E; kk <<= 1) {
+        regs_flip<E>(v, kk);
+#pragma unroll
+        for (int j = kk >> 2; j >= 1; j >>= 1) regs_half<E>(v, j);
+    }
+    const uint32_t tmax = (((1u << log2_ceil(n)) + E - 1) / E);   // threads holding real samples, a power of two
+    for (uint32_t kt = 2; kt <= tmax; kt <<= 1) {
+        regs_cross<E>(v, tid, kt - 1, true, a);
+        for (uint32_t jt = kt >> 2; jt >= 1; jt >>= 1) regs_cross<E>(v, tid, jt, false, a);
+#pragma unroll
+        for (int j = E >> 1; j >= 1; j >>= 1) regs_half<E>(v, j);
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) { const uint32_t g = tid * E + e; if (g < n) a[g] = v[e]; }
+    __syncthreads();
+}
+// Bitonic clean-up of a half-cleaned block of 512 * E slots: thread strides jt0 .. 1, then the in-register strides.
+template <int E>
+__device__ void clean_regs(float* a, uint32_t n, uint32_t tid, uint32_t jt0) {
+    float v[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) { const uint32_t g = tid * E + e; v[e] = g < n ? a[g] : __int_as_float(0x7f800000); }
+    __syncthreads();
+    for (uint32_t jt = jt0; jt >= 1; jt >>= 1) regs_cross<E>(v, tid, jt, false, a);
+#pragma unroll
+    for (int j = E >> 1; j >= 1; j >>= 1) regs_half<E>(v, j);
+#pragma unroll
+    for (int e = 0; e < E; ++e) { const uint32_t g = tid * E + e; if (g < n) a[g] = v[e]; }
+    __syncthreads();
+}
+__device__ void sort_small(float* a, uint32_t n, uint32_t tid) {           // n <= 16384, a in shared memory (>= 512 floats)
+    const uint32_t np2 = 1u << log2_ceil(n);
+    if (np2 <= 512) sort_regs<1>(a, n, tid);
+    else if (np2 <= 1024) sort_regs<2>(a, n, tid);
+    else if (np2 <= 2048) sort_regs<4>(a, n, tid);
+    else if (np2 <= 4096) sort_regs<8>(a, n, tid);
+    else if (np2 <= 8192) sort_regs<16>(a, n, tid);
+    else {
+        // 8192 < n <= 16384: both halves in registers, then the last merge — its flip and its
+        // stride-4096 step in shared memory, the rest (strides 2048 .. 1) per half in registers.
+        sort_regs<16>(a, 8192, tid);
+        sort_regs<16>(a + 8192, n - 8192, tid);
+        flip_step(a, n, 14, 8192, tid);
+        __syncthreads();
+        half_step(a, n, 12, 8192, tid);
+        __syncthreads();
+        clean_regs<16>(a, 8192, tid, 128);
+        clean_regs<16>(a + 8192, n - 8192, tid, 128);
+    }
+}
+
+// Ascending-order fp32 sum of s[0..m) by ONE thread (the rounding sequence of the reference's
+// sequential sum); 128-bit shared-memory loads keep the dependent FADD chain fed.
+__device__ __forceinline__ float seq_sum_shared(const float* s, uint32_t i0, uint32_t i1, float acc) {
+    uint32_t i = i0;
+    for (; i < i1 && (i & 3u); ++i) acc = __fadd_rn(acc, s[i]);
+    for (; i + 4 <= i1; i += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(s + i);
+        acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v.x), v.y), v.z), v.w);
+    }
+    for (; i < i1; ++i) acc = __fadd_rn(acc, s[i]);
+    return acc;
+}
+
+// One detection: the whole CTA works on (frame, slot).  Every branch below is CTA-uniform.
+__device__ void distance_item(const DistK& k, uint32_t frame, uint32_t slot, float* sbuf) {
     __shared__ uint32_t s_cnt, s_lo, s_hi, s_slot;
     __shared__ float s_acc;
     const uint32_t tid = threadIdx.x, lane = tid & 31;
-    const uint32_t frame = blockIdx.y, slot = blockIdx.x;
     float* outp = k.out + (size_t)frame * k.max_det + slot;
-    const uint32_t count = min(k.counts ? k.counts[frame] : k.max_det, k.max_det);
-    if (slot >= count) { if (tid == 0) *outp = -1.0f; return; }
 
     // bbox -> depth-map window, object_analysis.rs:238-253 (f32 divide, multiply, round half
     // away from zero, saturating `as u32`; i32 additions wrap as in a release build)
@@ -276,7 +388,7 @@ __global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const 
     if (big) {
         if (!k.scratch) { if (tid == 0) *outp = __int_as_float(0x7fc00000); return; }   // launcher guarantees scratch
         if (tid == 0) {
-            uint32_t s = (blockIdx.x + blockIdx.y) % kDistSlots;
+            uint32_t s = (frame + slot) % kDistSlots;
             while (atomicCAS(&k.locks[s], 0u, 1u) != 0u) { s = (s + 1) % kDistSlots; __nanosleep(200); }
             __threadfence();
             s_slot = s;
@@ -304,7 +416,7 @@ __global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const 
     // sort ascending (:265)
     const uint32_t ln = log2_ceil(n);
     if (!big) {
-        sort_shared(a, n, ln, tid);
+        sort_small(a, n, tid);
     } else {
         const uint32_t lc = log2_ceil(k.smem_floats);           // smem_floats is a power of two here
         const uint32_t ch = 1u << lc, nch = (n + ch - 1) >> lc;
@@ -356,8 +468,7 @@ __global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const 
     // mean in ascending order, one thread: the fp32 rounding sequence of `iter().sum::<f32>()` (:273-275)
     if (!big) {
         if (tid == 0) {
-            float acc = 0.0f;
-            for (uint32_t i = i0; i < i1; ++i) acc = __fadd_rn(acc, a[i]);
+            const float acc = seq_sum_shared(sbuf, i0, i1, 0.0f);
             *outp = i1 > i0 ? __fdiv_rn(acc, __uint2float_rn(i1 - i0)) : -1.0f;
         }
     } else {
@@ -367,11 +478,7 @@ __global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const 
             __syncthreads();
             for (uint32_t i = tid; i < m; i += kDistThreads) sbuf[i] = a[c0 + i];
             __syncthreads();
-            if (tid == 0) {
-                float acc = s_acc;
-                for (uint32_t i = 0; i < m; ++i) acc = __fadd_rn(acc, sbuf[i]);
-                s_acc = acc;
-            }
+            if (tid == 0) s_acc = seq_sum_shared(sbuf, 0, m, s_acc);
         }
         __syncthreads();
         if (tid == 0) {
@@ -379,6 +486,52 @@ __global__ void __launch_bounds__(kDistThreads) detection_distance_kernel(const 
             __threadfence();
             atomicExch(&k.locks[s_slot], 0u);
         }
+    }
+}
+
+// Persistent CTAs over the flattened list of real detections of frames [frame0, frame0 + nf):
+// the per-frame counts are prefix-summed in shared memory, items are handed out dynamically,
+// and the unused slots of the output are filled with -1 on the side.
+__global__ void __launch_bounds__(kDistThreads, 2) detection_distance_kernel(const DistK k, uint32_t frame0, uint32_t nf) {
+    extern __shared__ __align__(16) float sbuf[];
+    __shared__ uint32_t pre[kDistFrames + 1];
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t f = tid; f < nf; f += kDistThreads)
+        pre[f + 1] = min(k.counts ? k.counts[frame0 + f] : k.max_det, k.max_det);
+    if (tid == 0) pre[0] = 0;
+    __syncthreads();
+    if (tid < 32) {                                    // inclusive scan of pre[1..nf] by one warp, 32 at a time
+        uint32_t carry = 0;
+        for (uint32_t b = 0; b < nf; b += 32) {
+            const uint32_t f = b + tid;
+            uint32_t v = f < nf ? pre[f + 1] : 0u;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+                if ((int)tid >= o) v += u;
+            }
+            if (f < nf) pre[f + 1] = v + carry;
+            carry += __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+    // unused slots -> -1
+    for (size_t i = (size_t)blockIdx.x * kDistThreads + tid; i < (size_t)nf * k.max_det; i += (size_t)gridDim.x * kDistThreads) {
+        const uint32_t f = (uint32_t)(i / k.max_det), sl = (uint32_t)(i % k.max_det);
+        if (sl >= pre[f + 1] - pre[f]) k.out[(size_t)(frame0 + f) * k.max_det + sl] = -1.0f;
+    }
+    // Items cost anything from a few hundred to 16 K samples: CTAs draw them from a ticket counter.
+    __shared__ uint32_t s_item;
+    const uint32_t total = pre[nf];
+    for (;;) {
+        __syncthreads();                               // the previous item's shared state is dead
+        if (tid == 0) s_item = atomicAdd(k.ticket, 1u);
+        __syncthreads();
+        const uint32_t item = s_item;
+        if (item >= total) break;
+        uint32_t lo = 0, hi = nf;                      // largest f with pre[f] <= item
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (pre[mid] <= item) lo = mid; else hi = mid; }
+        distance_item(k, frame0 + lo, item - pre[lo], sbuf);
     }
 }
 
@@ -397,14 +550,14 @@ extern "C" tk_error_code_t tk_kernels_detection_distance(const tk_b200_distance_
     if (p->depth_width == 0 || p->depth_height == 0 || p->frame_width == 0 || p->frame_height == 0)
         return TK_ERROR_INVALID_DIMENSIONS;
     const unsigned long long n = (unsigned long long)p->depth_width * p->depth_height;
-    if (n > 0x7fffffffull || p->num_frames > 65535) return TK_ERROR_INVALID_DIMENSIONS;
+    if (n > 0x7fffffffull) return TK_ERROR_INVALID_DIMENSIONS;
     const DeviceInfo* dev = device_info();
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
     DistK k{};
     k.dets = p->d_detections; k.counts = p->d_num_detections; k.depth = p->d_depth_maps; k.out = p->d_distances;
     k.num_frames = p->num_frames; k.max_det = p->max_detections;
     k.depth_w = p->depth_width; k.depth_h = p->depth_height; k.frame_w = p->frame_width; k.frame_h = p->frame_height;
-    uint32_t cap = 64;
+    uint32_t cap = 512;                                    // >= one exchange slot per thread
     while (cap < n && cap < kDistChunk) cap <<= 1;
     k.smem_floats = cap;
     if (n > kDistChunk) {
@@ -420,6 +573,21 @@ extern "C" tk_error_code_t tk_kernels_detection_distance(const tk_b200_distance_
     const size_t smem = (size_t)cap * 4;
     TK_CUDA_TRY(cudaFuncSetAttribute(detection_distance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 TK_ERROR_GPU_CUDA_ERROR);
-    detection_distance_kernel<<<dim3(p->max_detections, p->num_frames), kDistThreads, smem, stream>>>(k);
-    return launch_status("detection_distance_kernel");
+    uint32_t per_sm = (uint32_t)((size_t)200 * 1024 / (smem + 8 * 1024));
+    per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / kDistThreads ? 2048 / kDistThreads : per_sm);
+    const uint32_t launches = (p->num_frames + kDistFrames - 1) / kDistFrames;
+    uint32_t* tickets = nullptr;                           // one counter per launch, stream-ordered lifetime
+    TK_CUDA_TRY(cudaMallocAsync(reinterpret_cast<void**>(&tickets), 4 * (size_t)launches, stream), TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED);
+    TK_CUDA_TRY(cudaMemsetAsync(tickets, 0, 4 * (size_t)launches, stream), TK_ERROR_GPU_CUDA_ERROR);
+    tk_error_code_t rc = TK_SUCCESS;
+    for (uint32_t f0 = 0; f0 < p->num_frames && rc == TK_SUCCESS; f0 += kDistFrames) {
+        k.ticket = tickets + f0 / kDistFrames;
+        const uint32_t nf = p->num_frames - f0 < kDistFrames ? p->num_frames - f0 : kDistFrames;
+        unsigned long long items = (unsigned long long)nf * p->max_detections;
+        const unsigned long long cap = (unsigned long long)dev->sm_count * per_sm;
+        detection_distance_kernel<<<(unsigned)(items < cap ? items : cap), kDistThreads, smem, stream>>>(k, f0, nf);
+        rc = launch_status("detection_distance_kernel");
+    }
+    cudaFreeAsync(tickets, stream);
+    return rc;
 }
