@@ -100,10 +100,39 @@ def other_kernels():
           f"{us:.1f} us/launch = {nf * 56 / us:.2f} detections/us (latency-bound, shared-memory sort)")
 
 
+def detect_latency():
+    """BASELINE config 0 through the reference's own call: tk_object_detector_detect on one HOST 640x480 frame
+    (upload + pre-process + bound network + decode + NMS + results), wall clock per call.  The network is a stand-in
+    (device-to-device copy of a prepared 25200x85 head tensor, enqueued from a Python ctypes callback)."""
+    import ctypes as C
+    cu = C.CDLL("libcuda.so.1")
+    print("\n| frame | detect() wall us (median of 200) | p90 us | detections |")
+    print("|---|---|---|---|")
+    for (w, h) in ((640, 480), (1920, 1080), (3840, 2160)):
+        frame = synth.rgb_frame(w, h, 0)
+        lg = torch.from_numpy(synth.logits_tensor(0)).cuda()
+
+        def net(d_in, n, iw, ih, d_out, p, l, stream):
+            return cu.cuMemcpyDtoDAsync_v2(C.c_uint64(d_out), C.c_uint64(lg.data_ptr()), C.c_size_t(n * p * l * 4), C.c_void_p(stream))
+
+        with V.ObjectDetector(class_labels=[f"c{i}" for i in range(80)]) as det:
+            det.bind_network(net, 25200)
+            for _ in range(10):
+                r = det.detect(frame)
+            ts = []
+            for _ in range(200):
+                t0 = time.perf_counter(); r = det.detect(frame); ts.append((time.perf_counter() - t0) * 1e6)
+            ts.sort()
+            print(f"| {w}x{h} RGB8 (pageable host memory) | {ts[100]:.0f} | {ts[180]:.0f} | {len(r)} |")
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "others":
+    if len(sys.argv) > 1 and sys.argv[1] == "detect":
+        detect_latency()
+    elif len(sys.argv) > 1 and sys.argv[1] == "others":
         other_kernels()
     else:
         pre_geometry()
         batch_sweep()
         other_kernels()
+        detect_latency()
