@@ -47,6 +47,19 @@ LOGIT_BYTES = P * (5 + NC) * 4
 ALG_PRE = FRAME_BYTES + TENSOR_BYTES_F16          # 8 678 400 B / frame
 ALG_POST = LOGIT_BYTES                            # 8 568 000 B / frame
 CONF_THR, IOU_THR, MAX_DET = 0.5, 0.5, 500        # tests/tk_vision_full_test.c:67, tk_vision_pipeline.c:376-377
+I420 = False
+SRC_NAME = "1080p RGB8"
+
+
+def set_workload(name: str) -> None:
+    """Default = BASELINE.json configs[1]+[2] (the metric's configuration).  "4k-i420" = configs[3]: 4K planar
+    YUV420 camera frames (src/ffi/c_api/tk_ffi_api.c:917-931) through the full pre + post pipeline."""
+    global SRC_W, SRC_H, FRAME_BYTES, ALG_PRE, I420, METRIC, SRC_NAME
+    if name == "4k-i420":
+        SRC_W, SRC_H, I420, SRC_NAME = 3840, 2160, True, "4K I420"
+        FRAME_BYTES = SRC_W * SRC_H * 3 // 2
+        METRIC = "frames/s (pre+decode+NMS, 4K I420->640^2)"
+    ALG_PRE = FRAME_BYTES + TENSOR_BYTES_F16
 
 
 def log(*a):
@@ -56,10 +69,10 @@ def log(*a):
 def make_inputs(batch: int, seed0: int):
     """Seeded synthetic batch: `batch` random 1080p RGB8 frames + `batch` detector-head tensors."""
     import synth
-    frames = np.empty((batch, SRC_H, SRC_W, 3), np.uint8)
+    frames = np.empty((batch, FRAME_BYTES), np.uint8) if I420 else np.empty((batch, SRC_H, SRC_W, 3), np.uint8)
     logits = np.empty((batch, P, 5 + NC), np.float32)
     for i in range(batch):
-        frames[i] = synth.rgb_frame(SRC_W, SRC_H, seed0 + i)
+        frames[i] = synth.i420_frame(SRC_W, SRC_H, seed0 + i) if I420 else synth.rgb_frame(SRC_W, SRC_H, seed0 + i)
         logits[i] = synth.logits_tensor(seed0 + i, adversarial=(i == 0))
     return frames, logits
 
@@ -89,11 +102,16 @@ class CpuPath:
             t.out = np.empty((3, DST, DST), np.float32)
             t.cand = np.zeros(4096, self.O.CAND_DTYPE)
             t.kept = np.zeros(MAX_DET, self.O.CAND_DTYPE)
+            t.rgb = np.empty((SRC_H, SRC_W, 3), np.uint8) if I420 else None
         return t
 
     def one(self, frame: np.ndarray, logits: np.ndarray) -> int:
         t = self._bufs()
         O = self.O
+        if I420:      # the reference has no YUV arithmetic: the oracle's BT.601 conversion, then its pre-processor
+            self.lib.oracle_i420_to_rgb8(frame.ctypes.data_as(C.c_void_p), C.c_uint32(SRC_W), C.c_uint32(SRC_H),
+                                         t.rgb.ctypes.data_as(C.c_void_p))
+            frame = t.rgb
         if self.ref is not None:
             vf = O._VideoFrame(SRC_W, SRC_H, SRC_W * 3, 0, frame.ctypes.data)
             rc = self.ref.tk_preprocessor_resize_and_normalize_to_chw(
@@ -119,7 +137,7 @@ class CpuPath:
         pre = ("reference tk_preprocessor_resize_and_normalize_to_chw compiled from the reference tree (oracle/_ref, "
                "gcc -O2 -mavx, fp32 CHW out)" if self.kind == "reference"
                else "C restatement of the reference pre-processor (oracle/, fp32 CHW out)")
-        return (f"{frames_done} frames of the bench workload (1080p RGB8 -> 640x640 + 25200x85 decode + class-wise NMS), "
+        return (f"{frames_done} frames of the bench workload ({SRC_NAME} -> 640x640 + 25200x85 decode + class-wise NMS), "
                 f"{pre} + CPU restatement of decode/NMS (the reference's postprocess_detections is a stub), "
                 f"one frame per thread, {self.threads} threads")
 
@@ -201,7 +219,7 @@ class ClockSampler:
 # Reference arm                                                                 #
 # --------------------------------------------------------------------------- #
 def config_dict(n_gpus: int, batch: int) -> dict:
-    return {"workload": f"1080p RGB8 x{batch} per GPU -> 640x640 fp16 NCHW (stretch-bilinear, ImageNet mean/std) + "
+    return {"workload": f"{SRC_NAME} x{batch} per GPU -> 640x640 fp16 NCHW (stretch-bilinear, ImageNet mean/std) + "
                         f"decode(raw, conf>{CONF_THR}) + class-wise NMS(IoU>{IOU_THR}, max {MAX_DET}) of {batch} tensors 25200x85 fp32",
             "frames_per_gpu": batch, "global_batch": batch * n_gpus, "src": [SRC_W, SRC_H], "dst": [DST, DST],
             "proposals": P, "classes": NC, "sharding": f"frames x{n_gpus}, no collective",
@@ -284,6 +302,7 @@ def run_b200(args) -> None:
     d_logits = h_logits.to(dev)
 
     pipe = V.Pipeline(device_id=local, max_batch=B, chunk_frames=args.chunk, width=SRC_W, height=SRC_H,
+                      fmt=V.PIXEL_I420 if I420 else V.PIXEL_RGB8,
                       tensor_w=DST, tensor_h=DST, out_dtype=torch.float16, num_proposals=P, num_classes=NC,
                       act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR, max_detections=MAX_DET,
                       stage_host_logits=args.stage_logits)
@@ -354,7 +373,7 @@ def run_b200(args) -> None:
         names = ["preprocess_kernel", "decode_kernel", "nms_kernel"]
         alg = [ALG_PRE * B, ALG_POST * B, 0]
         per_launch_ms = [m / max(calls, 1) for m in stage_ms]
-        traffic = load_traffic()
+        traffic = {} if I420 else load_traffic()          # the ncu capture is of the default workload
         stages = []
         for nme, a, m in zip(names, alg, per_launch_ms):
             ach = a / (m * 1e-3) / 1e9 if m > 0 and a else None
@@ -370,7 +389,8 @@ def run_b200(args) -> None:
         step_ach = (ALG_PRE + ALG_POST) * B / (step_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": "frames/s", "n_gpus": world,
                 "steps": K, "warmup": max(W, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f16 lerp -> f16 tensor (pre-process, within the 1e-2 fp16 bar); f32 / i32 (decode, NMS, bit-exact)",
+                "vs_baseline": None, "dtype": ("i32 BT.601 + f32 lerp -> f16 tensor (pre-process); f32 / i32 (decode, NMS, bit-exact)" if I420 else
+                          "f16 lerp -> f16 tensor (pre-process, within the 1e-2 fp16 bar); f32 / i32 (decode, NMS, bit-exact)"),
                 "data": "synthetic", "config": config_dict(world, B),
                 "roofline": roofline, "roofline_stages": stages,
                 "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
@@ -404,12 +424,17 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="frames per GPU per step")
+    ap.add_argument("--workload", default="1080p-rgb", choices=["1080p-rgb", "4k-i420"],
+                    help="1080p-rgb: BASELINE configs[1]+[2], the metric's configuration (default); 4k-i420: configs[3]")
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default 64; 32 for 4k-i420)")
     ap.add_argument("--chunk", type=int, default=8, help="frames per in-flight chunk of the host-buffer call")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-logits", action="store_true", help="e2e: copy the logits to HBM instead of decoding them in place")
     args = ap.parse_args()
+    set_workload(args.workload)
+    if args.batch <= 0:
+        args.batch = 32 if I420 else 64
     if args.impl == "reference":
         run_reference(args)
     else:
