@@ -99,13 +99,16 @@ __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, c
             const uint8_t* row = (k & 2) ? row1 : row0;
             int x = xb + (k & 1);
             int cx = min(x >> 1, cw - 1);
-            int yy = row[x];
-            int u = (int)row[p.u_slot_off + cx] - 128;
-            int v = (int)row[p.v_slot_off + cx] - 128;
-            int r = (yy * 65536 + 91881 * v + 32768) >> 16;
-            int g = (yy * 65536 - 22554 * u - 46802 * v + 32768) >> 16;
-            int b = (yy * 65536 + 116130 * u + 32768) >> 16;
-            r = min(max(r, 0), 255); g = min(max(g, 0), 255); b = min(max(b, 0), 255);
+            // (yy*65536 + K*(c-128) + 32768) >> 16 == yy + ((K*c + 32768 - 128*K) >> 16): the luma term is a
+            // multiple of 65536 and >> is a floor.  add + clamp to [0, 255] is one VIADDMNMX.RELU (DPX).
+            const int yy = row[x];
+            const int u = row[p.u_slot_off + cx], v = row[p.v_slot_off + cx];
+            const int dr = (91881 * v + (32768 - 128 * 91881)) >> 16;
+            const int dg = (-22554 * u - 46802 * v + (32768 + 128 * (22554 + 46802))) >> 16;
+            const int db = (116130 * u + (32768 - 128 * 116130)) >> 16;
+            const int r = __viaddmin_s32_relu(yy, dr, 255);
+            const int g = __viaddmin_s32_relu(yy, dg, 255);
+            const int b = __viaddmin_s32_relu(yy, db, 255);
             m[k][0] = __uint_as_float(0x4B000000u | (uint32_t)r);
             m[k][1] = __uint_as_float(0x4B000000u | (uint32_t)g);
             m[k][2] = __uint_as_float(0x4B000000u | (uint32_t)b);
