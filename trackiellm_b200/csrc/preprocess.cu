@@ -55,6 +55,7 @@ struct PreK {
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
     uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
+    float one;              // 1.0f at run time (see sum2)
 };
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
@@ -138,6 +139,55 @@ __device__ __forceinline__ float blend_norm(const PreK& p, int c, float m1, floa
         float bot = __fmaf_rn(xd, m4 - m3, m3 - kBias);
         float v = __fmaf_rn(yd, bot - top, top);
         return __fmaf_rn(v, p.fscale[c], p.fbias[c]);
+    }
+}
+
+// The same arithmetic for one channel of TWO neighbouring output pixels at once, in packed fp32
+// (FADD2 / FMUL2 / FFMA2, sm_100: two IEEE round-to-nearest lanes per issued instruction) — every
+// lane performs exactly the scalar sequence above, so the results are bit-identical to it.
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 f2s(float a) { return make_float2(a, a); }
+// ptxas 12.9 contracts a packed multiply followed by a packed add into FFMA2 even for mul.rn.f32x2 /
+// add.rn.f32x2 and under -fmad=false (seen in SASS; results then differ from the reference by an ulp).
+// An add whose operand is a product is therefore written as sum2(): fma(x, 1.0, y) with the 1.0 read
+// from the kernel parameters — one rounding of the exact sum, the same result as the add, nothing to contract.
+__device__ __forceinline__ unsigned long long pk(float2 a) {
+    unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y)); return r;
+}
+__device__ __forceinline__ float2 upk(unsigned long long r) {
+    float2 a; asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(r)); return a;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return upk(r);
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    unsigned long long r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return upk(r);
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c))); return upk(r);
+}
+__device__ __forceinline__ float2 sum2(float2 x, float2 y, float one) { return fma2(x, f2s(one), y); }
+template <bool EXACT>
+__device__ __forceinline__ float2 blend_norm2(const PreK& p, int c, float2 m1, float2 m2, float2 m3, float2 m4,
+                                              float2 xd, float2 omx, float yd, float omy) {
+    const float2 nb = f2s(-kBias);
+    if constexpr (EXACT) {
+        const float2 p1 = add2(m1, nb), p2 = add2(m2, nb), p3 = add2(m3, nb), p4 = add2(m4, nb);
+        const float2 yd2 = f2s(yd), omy2 = f2s(omy);
+        const float2 t1 = mul2(mul2(p1, omx), omy2);
+        const float2 t2 = mul2(mul2(p2, xd), omy2);
+        const float2 t3 = mul2(mul2(p3, omx), yd2);
+        const float2 t4 = mul2(mul2(p4, xd), yd2);
+        const float2 v = sum2(sum2(sum2(t1, t2, p.one), t3, p.one), t4, p.one);
+        const float2 t = sum2(mul2(v, f2s(1.0f / 255.0f)), f2s(-p.mean[c]), p.one);        // x - mean == x + (-mean)
+        const float2 q = mul2(t, f2s(p.rstd[c]));
+        const float2 r = fma2(q, f2s(-p.stdv[c]), t);                                  // -q*std == q*(-std)
+        return fma2(r, f2s(p.rstd[c]), q);
+    } else {
+        const float2 top = fma2(xd, add2(m2, f2(-m1.x, -m1.y)), add2(m1, nb));
+        const float2 bot = fma2(xd, add2(m4, f2(-m3.x, -m3.y)), add2(m3, nb));
+        const float2 v = fma2(f2s(yd), add2(bot, f2(-top.x, -top.y)), top);
+        return fma2(v, f2s(p.fscale[c]), f2s(p.fbias[c]));
     }
 }
 
@@ -432,16 +482,18 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
                     const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
                     const float xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (LBOX && xbs[j] < 0) {
-                            o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2];
-                        } else {
-                            float m[4][3];
-                            fetch_quad<FMT>(p, row0, row1, xbs[j], m);
-                            const float xd = xds[j], omx = __fsub_rn(1.0f, xd);
+                    for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
+                        float ma[4][3], mb[4][3];
+                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j], 0) : xbs[j], ma);
+                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
+                        const float2 xd2 = f2(xds[j], xds[j + 1]);
+                        const float2 omx2 = add2(f2s(1.0f), f2(-xd2.x, -xd2.y));      // 1 - xd
 #pragma unroll
-                            for (int c = 0; c < 3; ++c)
-                                o[c][j] = blend_norm<EXACT>(p, c, m[0][c], m[1][c], m[2][c], m[3][c], xd, omx, yd, omy);
+                        for (int c = 0; c < 3; ++c) {
+                            const float2 r = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
+                                                                f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2, omx2, yd, omy);
+                            o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : r.x;
+                            o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : r.y;
                         }
                     }
                 } else {
@@ -590,6 +642,7 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     k.x_ratio = ((float)k.src_w - 1.0f) / (float)k.new_w;
     k.y_ratio = ((float)k.src_h - 1.0f) / (float)k.new_h;
     k.swap_rb = bgr ? 1u : 0u;
+    k.one = 1.0f;
     for (int c = 0; c < 3; ++c) {
         // constants are indexed by SOURCE channel; BGR byte c is tensor channel 2 - c
         const int tc = bgr ? 2 - c : c;
