@@ -146,3 +146,38 @@ def test_cuda_tensor_nms_reference_signature():
             disp.free(b)
     assert n == len(ref)
     assert np.array_equal(idx[:n], ref["index"]) and np.all(idx[n:] == -1)
+
+
+def test_random_post_configs_bitexact():
+    """40 seeded random head shapes / thresholds / caps / activations / crowd densities — ragged proposal counts
+    (not multiples of the cluster slice), 1..91 classes, candidate caps that truncate, class-agnostic mode via
+    identical class ids — every kept record bit-for-bit against the oracle."""
+    rng = np.random.default_rng(77)
+    for case in range(40):
+        P = int(rng.integers(1, 30000))
+        C = int(rng.integers(1, 92))
+        act = (V.ACT_RAW, V.ACT_SIGMOID, V.ACT_SOFTMAX)[case % 3]
+        objects = int(rng.integers(0, 90))
+        dups = int(rng.integers(1, 30))
+        thr = float(rng.choice([0.25, 0.5, 0.5, 0.7]))
+        iou = float(rng.choice([0.3, 0.45, 0.5, 0.65]))
+        cap = int(rng.choice([64, 500, 4096, 4096]))
+        max_det = int(rng.choice([1, 20, 300, 500]))
+        agnostic = bool(case % 5 == 4)
+        n = int(rng.integers(1, 4))
+        ts = np.stack([synth.logits_tensor(9000 + 10 * case + i, num_proposals=P, num_classes=C, objects=objects, dups=dups,
+                                           adversarial=(P >= 64 and i == 0), as_logit=(act != V.ACT_RAW)) for i in range(n)])
+        got = full_post(ts, thr, iou, max_det, act, cap=cap, agnostic=agnostic)
+        for i in range(n):
+            c, total = O.decode(ts[i], thr, act, cap=cap)
+            if agnostic:
+                c = c.copy()
+                cls = c["class_id"].copy()
+                c["class_id"] = 0
+                ref = O.nms_classwise(c, iou, max_det)
+                # the oracle ran on class 0; put the real class ids back by proposal index
+                back = {int(k): int(v) for k, v in zip(c["index"], cls)}
+                ref["class_id"] = [back[int(k)] for k in ref["index"]]
+            else:
+                ref = O.nms_classwise(c, iou, max_det)
+            assert same(got[i], ref.view(V.CAND_DTYPE)), (case, P, C, act, objects, dups, thr, iou, cap, max_det, agnostic, i)
