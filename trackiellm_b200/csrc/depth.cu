@@ -11,9 +11,11 @@
 //   tk_kernels_detection_distance : per-detection robust distance,
 //       calculate_raw_distance of src/vision/src/object_analysis.rs:227-279
 //       (bbox -> depth window -> valid samples -> sort -> IQR filter -> mean).
-//       One CTA per detection; samples sorted in shared memory by a normalised
-//       bitonic network (any length, no padding), summed in ascending order by one
-//       thread so the fp32 result is bit-identical to the sequential reference.
+//       Persistent CTAs draw (frame, detection) items from a ticket counter; the samples of an item are
+//       compacted into shared memory, sorted by a normalised bitonic network held in registers
+//       (in-thread min/max pairs, warp shuffles, shared memory only for the widest strides; any
+//       length, +inf padding), and summed in ascending order by one thread so the fp32 result is
+//       bit-identical to the sequential reference.
 #include "tk_common.cuh"
 
 #include <cooperative_groups.h>
