@@ -130,3 +130,26 @@ def test_detect_error_behaviour():
     hh = C.c_void_p()
     lib.tk_object_detector_destroy(C.byref(hh))                 # NULL handle is a no-op
     lib.tk_object_detector_update_thresholds(None, 0.1, 0.1)
+
+
+def test_detector_flow_from_c(tmp_path):
+    """The same call sequence from plain C (tests/c/tk_detector_flow_test.c, built by __graft_entry__.build()):
+    create -> bind network -> detect x2 -> free_results -> update_thresholds -> destroy, on a 640x480 frame."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(__file__), "c", "tk_detector_flow_test")
+    if not os.path.exists(exe):
+        pytest.fail("tests/c/tk_detector_flow_test is not built: run __graft_entry__.build()")
+    logits = synth.logits_tensor(4)
+    frame = synth.rgb_frame(640, 480, 4)
+    lp, fp = tmp_path / "logits.f32", tmp_path / "frame.rgb"
+    logits.tofile(lp)
+    frame.tofile(fp)
+    out = subprocess.run([exe, str(lp), str(synth.NUM_PROPOSALS), "80", str(fp), "640", "480"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    got = []
+    for line in out.stdout.splitlines():
+        c, label, bits, x, y, w, h = line.split()
+        got.append((int(c), label, int(bits, 16), (int(x), int(y), int(w), int(h))))
+    want = oracle_records(logits, 640, 480)
+    assert len(want) > 10 and got == want
