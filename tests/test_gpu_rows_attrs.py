@@ -42,6 +42,32 @@ def test_softmax_argmax_vs_oracle(rows, cols):
     assert np.max(np.abs(got - O.softmax_rows(x))) <= 1e-6   # libm-exp oracle == reference arithmetic
 
 
+@pytest.mark.parametrize("cols", [80, 81, 128, 12])
+def test_softmax_edge_rows_bitexact(cols):
+    """Rows that leave the fast paths: exponentials in the subnormal range and exact zeros (the Markstein
+    divide falls back to the IEEE divide), huge dynamic range, constant rows, infinities and NaNs (compared as
+    NaN-ness; arithmetic NaN payloads differ between x86 and the GPU), many rows so every tile position occurs."""
+    rng = np.random.default_rng(cols)
+    rows = 4099
+    x = rng.normal(0, 30, (rows, cols)).astype(np.float32)          # differences of +-100: exp spans 1 .. 0
+    x[1] = 0.0
+    x[2] = -1e30
+    x[3, :] = np.linspace(-110, 0, cols, dtype=np.float32)          # crosses the underflow threshold
+    x[4, 0] = np.inf
+    x[5, cols // 2] = -np.inf
+    x[6, 1] = np.nan
+    x[7, 0] = np.nan
+    x[8] = np.float32(88.0); x[8, -1] = np.float32(-15.5)
+    sm, am = V.argmax_rows(torch.from_numpy(x).cuda())
+    torch.cuda.synchronize()
+    got, ref = sm.cpu().numpy(), O.softmax_rows(x, det_exp=True)
+    assert np.array_equal(am.cpu().numpy().astype(np.uint32), O.argmax_rows(x))
+    assert np.array_equal(np.isnan(got), np.isnan(ref))
+    ok = ~np.isnan(ref)
+    assert np.array_equal(bits(got[ok]), bits(ref[ok]))
+    assert (got[ok] == 0).sum() > 1000 and ((got[ok] > 0) & (got[ok] < 1e-38)).sum() > 0   # zeros and subnormals were exercised
+
+
 def test_reference_softmax_test_program():
     exe = os.path.join(ROOT, "oracle", "_ref", "tk_gpu_softmax_test")
     if not os.path.exists(exe):

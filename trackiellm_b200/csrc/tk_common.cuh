@@ -95,6 +95,30 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
         ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+
+// ---- packed fp32 (sm_100: two IEEE round-to-nearest lanes per issued instruction) ----------------
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 f2s(float a) { return make_float2(a, a); }
+// ptxas 12.9 contracts a packed multiply followed by a packed add into FFMA2 even for mul.rn.f32x2 /
+// add.rn.f32x2 and under -fmad=false (seen in SASS; results then differ from the reference by an ulp).
+// An add whose operand is a product is therefore written as sum2(): fma(x, 1.0, y) with the 1.0 read
+// from the kernel parameters — one rounding of the exact sum, the same result as the add, nothing to contract.
+__device__ __forceinline__ unsigned long long pk(float2 a) {
+    unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y)); return r;
+}
+__device__ __forceinline__ float2 upk(unsigned long long r) {
+    float2 a; asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(r)); return a;
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return upk(r);
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+    unsigned long long r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return upk(r);
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c))); return upk(r);
+}
+__device__ __forceinline__ float2 sum2(float2 x, float2 y, float one) { return fma2(x, f2s(one), y); }
 #endif
 
 }  // namespace tkb
