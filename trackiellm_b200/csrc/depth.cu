@@ -65,12 +65,21 @@ __global__ void __launch_bounds__(kMetricThreads) inverse_depth_metric_kernel(co
     // `if (d < min) min = d` never takes a NaN (tk_depth_midas.c:479-482); fminf/fmaxf drop NaNs likewise.
     float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
     if (k.vec) {
-        for (uint32_t i = lo + 4 * tid; i < hi; i += 4 * kMetricThreads) {
-            const float4 v = __ldcs(reinterpret_cast<const float4*>(in + i));
+        auto take = [&](uint32_t i, const float4 v) {
             if (i - lo < k.cache_floats) *reinterpret_cast<float4*>(cache + (i - lo)) = v;
             mn = fminf(fminf(mn, v.x), fminf(v.y, fminf(v.z, v.w)));
             mx = fmaxf(fmaxf(mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+        };
+        constexpr uint32_t S = 4 * kMetricThreads;
+        uint32_t i = lo + 4 * tid;
+        for (; i + 3 * S < hi; i += 4 * S) {                      // four 128-bit loads in flight per thread
+            const float4 a = __ldcs(reinterpret_cast<const float4*>(in + i));
+            const float4 b = __ldcs(reinterpret_cast<const float4*>(in + i + S));
+            const float4 c = __ldcs(reinterpret_cast<const float4*>(in + i + 2 * S));
+            const float4 d = __ldcs(reinterpret_cast<const float4*>(in + i + 3 * S));
+            take(i, a); take(i + S, b); take(i + 2 * S, c); take(i + 3 * S, d);
         }
+        for (; i < hi; i += S) take(i, __ldcs(reinterpret_cast<const float4*>(in + i)));
     } else {
         for (uint32_t i = lo + tid; i < hi; i += kMetricThreads) {
             const float v = in[i];

@@ -54,12 +54,23 @@ __global__ void __launch_bounds__(256) depth_scale_kernel(const float* __restric
     const size_t step = (size_t)gridDim.x * blockDim.x;
     if (vec) {
         const size_t n4 = n >> 2;
-        for (; i < n4; i += step) {
-            float4 v = __ldcs(reinterpret_cast<const float4*>(in) + i);
+        auto conv = [&](float4 v) {
             v.x = __fadd_rn(__fmul_rn(v.x, scale), shift); v.y = __fadd_rn(__fmul_rn(v.y, scale), shift);
             v.z = __fadd_rn(__fmul_rn(v.z, scale), shift); v.w = __fadd_rn(__fmul_rn(v.w, scale), shift);
-            __stcs(reinterpret_cast<float4*>(out) + i, v);
+            return v;
+        };
+        // four 128-bit loads in flight per thread before the first store: enough bytes outstanding per SM for HBM3e
+        for (; i + 3 * step < n4; i += 4 * step) {
+            const float4 a = __ldcs(reinterpret_cast<const float4*>(in) + i);
+            const float4 b = __ldcs(reinterpret_cast<const float4*>(in) + i + step);
+            const float4 c = __ldcs(reinterpret_cast<const float4*>(in) + i + 2 * step);
+            const float4 d = __ldcs(reinterpret_cast<const float4*>(in) + i + 3 * step);
+            __stcs(reinterpret_cast<float4*>(out) + i, conv(a));
+            __stcs(reinterpret_cast<float4*>(out) + i + step, conv(b));
+            __stcs(reinterpret_cast<float4*>(out) + i + 2 * step, conv(c));
+            __stcs(reinterpret_cast<float4*>(out) + i + 3 * step, conv(d));
         }
+        for (; i < n4; i += step) __stcs(reinterpret_cast<float4*>(out) + i, conv(__ldcs(reinterpret_cast<const float4*>(in) + i)));
         i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     }
     for (; i < n; i += step) out[i] = __fadd_rn(__fmul_rn(in[i], scale), shift);
@@ -79,20 +90,20 @@ __global__ void __launch_bounds__(256) depth_points_kernel(const float* __restri
     size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (vec) {
         const size_t n4 = n >> 2;
-        for (; q < n4; q += step) {
-            const float4 d4 = __ldcs(reinterpret_cast<const float4*>(depth) + q);
+        auto emit = [&](size_t qq, const float4 d4) {
             const float ds[4] = {d4.x, d4.y, d4.z, d4.w};
             float o[12];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const size_t idx = q * 4 + j;
+                const size_t idx = qq * 4 + j;
                 unproject(ds[j], (uint32_t)(idx % W), (uint32_t)(idx / W), fx, fy, cx, cy, o + 3 * j);
             }
-            float4* dst = reinterpret_cast<float4*>(pts) + q * 3;
+            float4* dst = reinterpret_cast<float4*>(pts) + qq * 3;
             __stcs(dst + 0, make_float4(o[0], o[1], o[2], o[3]));
             __stcs(dst + 1, make_float4(o[4], o[5], o[6], o[7]));
             __stcs(dst + 2, make_float4(o[8], o[9], o[10], o[11]));
-        }
+        };
+        for (; q < n4; q += step) emit(q, __ldcs(reinterpret_cast<const float4*>(depth) + q));
         q = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     }
     for (; q < n; q += step) unproject(depth[q], (uint32_t)(q % W), (uint32_t)(q / W), fx, fy, cx, cy, pts + 3 * q);
