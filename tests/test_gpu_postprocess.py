@@ -115,6 +115,36 @@ def test_nms_idempotent_on_gpu():
     assert same(V.candidates_to_numpy(d, m)[0], V.candidates_to_numpy(d2, m2)[0])
 
 
+def test_nms_more_frames_than_sms_mixed_sizes():
+    """Batches above the SM count take the two-launch path (frames of <= 512 candidates with 25 KB of shared
+    memory, looping CTAs; the crowded frames in a second launch): candidate counts below, at and above the split,
+    empty frames, a count above the cap — every frame against the oracle."""
+    rng = np.random.default_rng(77)
+    n, cap = 700, 2048
+    sizes = rng.choice([0, 1, 63, 64, 65, 300, 511, 512, 513, 900, 2048, 2500], n)
+    host = np.zeros((n, cap), O.CAND_DTYPE)
+    refs = []
+    for f, k in enumerate(sizes):
+        kk = min(int(k), cap)
+        c = np.zeros(kk, O.CAND_DTYPE)
+        c["index"] = np.sort(rng.choice(25200, kk, replace=False))
+        cx, cy = rng.uniform(0, 640, kk), rng.uniform(0, 640, kk)
+        if kk > 600:                                       # a crowd of one class: the blocked path
+            cx, cy = rng.normal(320, 40, kk), rng.normal(320, 40, kk)
+        w, h = rng.uniform(8, 200, kk), rng.uniform(8, 200, kk)
+        c["x"], c["y"], c["w"], c["h"] = (cx - w / 2).astype(np.int32), (cy - h / 2).astype(np.int32), w.astype(np.int32), h.astype(np.int32)
+        c["confidence"] = rng.choice(np.linspace(0.5, 1.0, 97, dtype=np.float32), kk)   # many exact ties
+        c["class_id"] = rng.integers(0, 3 if kk > 600 else 80, kk)
+        host[f, :kk] = c
+        refs.append(O.nms_classwise(c, 0.5, 300))
+    cands = torch.from_numpy(host.view(np.int32).reshape(n, cap, V.CAND_WORDS)).cuda()
+    counts = torch.from_numpy(sizes.astype(np.int32)).cuda()
+    dets, ndet = V.nms_classwise(cands, counts, 0.5, 300)
+    got = V.candidates_to_numpy(dets, ndet)
+    for f in range(n):
+        assert same(got[f], refs[f].view(V.CAND_DTYPE)), (f, int(sizes[f]))
+
+
 def test_nms_empty_frames():
     ts = np.stack([synth.logits_tensor(8), synth.logits_tensor(9)])
     ts[1, :, 4] = 0.0

@@ -135,6 +135,20 @@ def test_depth_kernels():
     assert np.array_equal(bits(pts), bits(ref))
 
 
+@pytest.mark.parametrize("h,w", [(1, 1), (7, 3), (9, 4), (33, 5), (64, 7), (3, 4099), (1031, 1283), (2, 70001)])
+def test_point_cloud_shapes_bitexact(h, w):
+    """Widths below, at and far above the four points a thread makes; grids that wrap rows several times per step."""
+    rng = np.random.default_rng(h * 7 + w)
+    raw = rng.uniform(-50, 1100, (h, w)).astype(np.float32)
+    raw.flat[:: 17] = 0.0
+    fx, fy, cx, cy = np.float32(517.3), np.float32(311.7), np.float32(w / 2.0 - 0.25), np.float32(h / 3.0)
+    pts = V.kernels_depth_to_point_cloud(torch.from_numpy(raw).cuda(), float(fx), float(fy), float(cx), float(cy)).cpu().numpy()
+    v, u = np.meshgrid(np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32), indexing="ij")
+    ok = (raw > 0) & (raw <= 1000)
+    ref = np.where(ok[..., None], np.stack([(u - cx) * raw / fx, (v - cy) * raw / fy, raw], axis=-1), 0).astype(np.float32)
+    assert np.array_equal(bits(pts), bits(ref))
+
+
 def test_dispatcher_roundtrip_and_preprocess():
     fr = synth.rgb_frame(640, 480, 0)
     out = np.empty((3, 640, 640), np.float32)

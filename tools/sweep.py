@@ -131,6 +131,8 @@ if __name__ == "__main__":
         detect_latency()
     elif len(sys.argv) > 1 and sys.argv[1] == "others":
         other_kernels()
+    elif len(sys.argv) > 1 and sys.argv[1] == "batch":
+        batch_sweep()
     else:
         pre_geometry()
         batch_sweep()

@@ -44,7 +44,11 @@ struct NmsK {
     int agnostic;
     int restore;
     float sx, sy;                   // src/in scale of the optional coordinate restore
+    uint32_t num_frames;
+    uint32_t select;                // 0: every frame; 1: only frames of <= kNmsSmall candidates; 2: only the others
 };
+
+static constexpr uint32_t kNmsSmall = 512;   // the register path's limit: 25 KB of shared memory per CTA instead of 200 KB
 
 // src/vision/src/object_analysis.rs:71-91 (i32 arithmetic wraps like release-mode Rust).
 __device__ __forceinline__ float iou_rect(int4 a, int4 b) {
@@ -115,7 +119,7 @@ __device__ __forceinline__ void bitonic_sort_regs512(unsigned long long& key, ui
     }
 }
 
-__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
+__device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame) {
     extern __shared__ __align__(16) uint8_t dsm[];
     __shared__ unsigned long long diag[64];
     __shared__ unsigned long long blk_kept;
@@ -123,11 +127,12 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
     __shared__ uint32_t warp_tot[kNmsWarps];
     __shared__ uint32_t seg_overflow;
 
-    const uint32_t frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const tk_b200_candidate_t* in = k.cands + (size_t)frame * k.cap;
     tk_b200_candidate_t* out = k.dets + (size_t)frame * k.max_det;
     const uint32_t K = min(k.counts[frame], k.cap);
     if (K == 0 || k.max_det == 0) { if (tid == 0) k.num_dets[frame] = 0; return; }
+    if ((k.select == 1 && K > kNmsSmall) || (k.select == 2 && K <= kNmsSmall)) return;    // the other launch's frame
     uint32_t Kp = 64;
     while (Kp < K) Kp <<= 1;                                       // sort only what this frame needs
 
@@ -347,6 +352,14 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const NmsK k) {
     if (tid == 0) k.num_dets[frame] = min(run, k.max_det);
 }
 
+// One CTA per frame while the batch fits one wave; larger batches loop (every exit of nms_frame is CTA-uniform).
+__global__ void __launch_bounds__(kNmsThreads, 3) nms_kernel(const NmsK k) {
+    for (uint32_t frame = blockIdx.x; frame < k.num_frames; frame += gridDim.x) {
+        nms_frame(k, frame);
+        __syncthreads();
+    }
+}
+
 }  // namespace tkb
 
 using namespace tkb;
@@ -376,9 +389,36 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
         k.sx = (float)p->restore_src_width / (float)p->restore_in_width;
         k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
     }
+    k.num_frames = p->num_frames;
     const size_t smem = nms_smem_bytes(k.Kp);
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
-    nms_kernel<<<p->num_frames, kNmsThreads, smem, stream>>>(k);
+    const uint32_t sms = (uint32_t)dev->sm_count;
+    if (p->num_frames <= sms || k.Kp <= kNmsSmall) {
+        // one wave (or the small layout anyway): a single launch sized for the cap
+        int per_sm = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_kernel, kNmsThreads, smem) != cudaSuccess || per_sm < 1) {
+            cudaGetLastError(); per_sm = 1;
+        }
+        const uint32_t cap = sms * (uint32_t)per_sm;
+        nms_kernel<<<p->num_frames < cap ? p->num_frames : cap, kNmsThreads, smem, stream>>>(k);
+        return launch_status("nms_kernel");
+    }
+    // More frames than SMs: shared memory sized for the cap (200 KB at 4096 candidates) means one CTA per SM and
+    // batch / 148 waves.  Frames of <= 512 candidates — the normal case — only use the register path, which needs
+    // 25 KB: they go first, several CTAs per SM; a second one-wave launch takes the crowded frames and skips the rest.
+    NmsK small = k;
+    small.Kp = kNmsSmall; small.select = 1;
+    const size_t smem_small = nms_smem_bytes(kNmsSmall);
+    int per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_kernel, kNmsThreads, smem_small) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError(); per_sm = 1;
+    }
+    const uint32_t cap_small = sms * (uint32_t)per_sm;
+    nms_kernel<<<p->num_frames < cap_small ? p->num_frames : cap_small, kNmsThreads, smem_small, stream>>>(small);
+    tk_error_code_t rc = launch_status("nms_kernel");
+    if (rc != TK_SUCCESS) return rc;
+    k.select = 2;
+    nms_kernel<<<sms, kNmsThreads, smem, stream>>>(k);
     return launch_status("nms_kernel");
 }

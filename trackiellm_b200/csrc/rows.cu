@@ -216,9 +216,13 @@ static tk_error_code_t launch_rows(const float* in, float* out, uint32_t* amax, 
         const bool vec = (cols % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
         auto kern = vec ? softmax_tile_kernel<true> : softmax_tile_kernel<false>;
         TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
-        const uint32_t per_sm = smem ? (uint32_t)((size_t)200 * 1024 / smem) : 8u;
+        int per_sm = 0;             // one wave of persistent CTAs: what registers AND the tile's shared memory let an SM hold
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRowThreads, smem) != cudaSuccess || per_sm < 1) {
+            cudaGetLastError();
+            per_sm = 1;
+        }
         uint32_t grid = (k.ntiles + kRowWarps - 1) / kRowWarps;
-        const uint32_t cap = (uint32_t)dev->sm_count * (per_sm ? per_sm : 1u);
+        const uint32_t cap = (uint32_t)dev->sm_count * (uint32_t)per_sm;
         if (grid > cap) grid = cap;
         kern<<<grid, kRowThreads, smem, stream>>>(k);
         return launch_status("softmax_tile_kernel");
@@ -226,8 +230,13 @@ static tk_error_code_t launch_rows(const float* in, float* out, uint32_t* amax, 
     const size_t smem = (size_t)kRowWarps * (cols <= kSeqMaxCols ? cols : kSeqMaxCols) * 4;
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(softmax_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, softmax_row_kernel, kRowThreads, smem) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        per_sm = 1;
+    }
     uint32_t grid = (rows + kRowWarps - 1) / kRowWarps;
-    const uint32_t cap = (uint32_t)dev->sm_count * 8u;
+    const uint32_t cap = (uint32_t)dev->sm_count * (uint32_t)per_sm;
     if (grid > cap) grid = cap;
     softmax_row_kernel<<<grid, kRowThreads, smem, stream>>>(k);
     return launch_status("softmax_row_kernel");
