@@ -305,7 +305,7 @@ def run_b200(args) -> None:
                       fmt=V.PIXEL_I420 if I420 else V.PIXEL_RGB8,
                       tensor_w=DST, tensor_h=DST, out_dtype=torch.float16, num_proposals=P, num_classes=NC,
                       act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR, max_detections=MAX_DET,
-                      stage_host_logits=args.stage_logits)
+                      stage_host_logits=args.logits_mode)
     d_tensor, d_dets, d_counts = pipe.alloc_outputs(B)
     _, h_dets, h_counts = pipe.alloc_outputs(B, pinned=True)
     lib = capi.lib()
@@ -331,6 +331,7 @@ def run_b200(args) -> None:
     stage_ms, calls = pipe.stage_times()
     pipe.stage_timing(0)
     dev_counts = d_counts.cpu().numpy().copy()
+    dev_cand_counts = (logits_np[:, :, 4] > CONF_THR).sum(axis=1)      # rows that pass the threshold (read in full by decode)
     dev_dets = d_dets.cpu().numpy().copy()
 
     # ---------------- end to end through the host-buffer C-ABI call: `e2e` ----------------
@@ -396,14 +397,19 @@ def run_b200(args) -> None:
                 "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
                                   "unit": "GB/s", "frac": step_ach / peak},
                 "e2e": {"value": world * B * Ke / e2e_s, "unit": "frames/s",
-                        "h2d_bytes_per_step": B * (FRAME_BYTES + (LOGIT_BYTES if args.stage_logits else 0)),
-                        "host_bytes_read_in_place_per_step": 0 if args.stage_logits else B * LOGIT_BYTES,
+                        "h2d_bytes_per_step": B * (FRAME_BYTES + (LOGIT_BYTES, P * 4, 0)[(1, 0, 2).index(args.logits_mode)]),
+                        "host_bytes_read_in_place_per_step": (0 if args.logits_mode == 1 else
+                                                              int(np.sum(np.minimum(dev_cand_counts, 4096))) * (5 + NC) * 4
+                                                              + (B * P * 64 if args.logits_mode == 2 else 0)),
                         "d2h_bytes_per_step": B * (MAX_DET * 28 + 4), "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke,
                         "api": "tk_b200_pipeline_process_host (pinned host frames + logits in, host detections + counts out; "
                                "the fp16 tensors stay on the device for the detector); frames are copied H2D in chunks, "
-                               + ("logits are copied H2D in chunks" if args.stage_logits else
-                                  "the pinned logits are read in place over PCIe by decode_kernel (objectness word of every "
-                                  "row + surviving rows), not copied")},
+                               + {1: "logits are copied H2D in chunks",
+                                  2: "the pinned logits are read in place over PCIe by decode_kernel (objectness word of every "
+                                     "row, 64 B per request, + surviving rows), not copied",
+                                  0: "the pinned logits stay in host memory: their objectness column (4 of every 340 bytes) is "
+                                     "packed by 4 host threads while the frame copies run and uploaded as one dense array; "
+                                     "decode_kernel reads only the surviving rows in place over PCIe"}[args.logits_mode]},
                 "e2e_device_logits": {"value": world * B * Ke / e2e_dl_s, "unit": "frames/s",
                                       "h2d_bytes_per_step": B * FRAME_BYTES, "d2h_bytes_per_step": B * (MAX_DET * 28 + 4),
                                       "api": "tk_b200_pipeline_process_host_frames (logits already in HBM)"},
@@ -430,7 +436,9 @@ def main() -> None:
     ap.add_argument("--chunk", type=int, default=8, help="frames per in-flight chunk of the host-buffer call")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--stage-logits", action="store_true", help="e2e: copy the logits to HBM instead of decoding them in place")
+    ap.add_argument("--logits-mode", type=int, default=0, choices=[0, 1, 2],
+                    help="e2e, host logits: 0 objectness column packed on the host + surviving rows in place (default), "
+                         "1 whole tensor copied to HBM, 2 objectness and rows read in place over PCIe")
     args = ap.parse_args()
     set_workload(args.workload)
     if args.batch <= 0:

@@ -286,9 +286,12 @@ typedef struct {
     uint32_t              max_detections;     /* post-NMS cap per frame; 0 = 500 (tk_object_detector.c:39) */
     int                   class_agnostic;
     int                   restore_coordinates; /* 1 = boxes returned in source-frame px          */
-    int                   stage_host_logits;  /* process_host: 0 = decode reads page-locked host logits in place
-                                                 over PCIe (pageable logits are always staged); 1 = always copy
-                                                 the tensor to HBM first                                         */
+    int                   stage_host_logits;  /* process_host with page-locked host logits (pageable logits are always
+                                                 staged): 0 = the rows stay in host memory — their objectness column
+                                                 is packed by host threads and copied as one dense array, decode reads
+                                                 only the surviving rows over PCIe; 1 = copy the whole tensor to HBM
+                                                 first; 2 = decode reads objectness words and surviving rows in place
+                                                 over PCIe (one read request per row)                              */
 } tk_b200_pipeline_config_t;
 
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out_pipeline, const tk_b200_pipeline_config_t* config);
@@ -306,9 +309,10 @@ TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_device(
 /* HOST inputs and outputs (pinned memory from tk_b200_host_alloc copies by DMA;
  * pageable memory works, slower).  The batch is cut into chunks; upload of chunk
  * k+1, compute of chunk k and download of chunk k-1 overlap on three streams
- * ordered by events.  Page-locked h_logits are not copied at all: decode reads
- * the objectness word of each row and the surviving rows in place over PCIe
- * (a tenth of the tensor), concurrently with the frame uploads.  h_logits may
+ * ordered by events.  Page-locked h_logits are not copied: the 4-byte objectness
+ * word of each 340-byte row is packed into a dense column on the host (threads,
+ * while the frame copies run) and uploaded, and decode reads only the surviving
+ * rows in place over PCIe — 2 % of the tensor crosses the link.  h_logits may
  * be NULL (pre-process only) and h_frames may be NULL (post-process only).  The model-input tensors stay on the device for
  * the detector (tk_b200_pipeline_tensor_device_ptr) and are also downloaded when
  * h_tensor != NULL.  Blocks until the outputs are in host memory. */

@@ -56,7 +56,7 @@ def test_process_device_vs_oracle():
         check_dets(d, c, logits)
 
 
-@pytest.mark.parametrize("stage", [False, True])     # logits read in place over PCIe / staged through HBM
+@pytest.mark.parametrize("stage", [0, 1, 2])     # objectness column packed on the host / tensor staged through HBM / read in place over PCIe
 @pytest.mark.parametrize("n,chunk", [(1, 1), (7, 3), (8, 8), (10, 4), (5, 16)])
 def test_process_host_matches_oracle_and_device(n, chunk, stage):
     frames, logits = inputs(n, seed0=10)

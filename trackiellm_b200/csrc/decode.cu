@@ -36,6 +36,8 @@ static constexpr int kDecWarps = kDecThreads / 32;
 
 struct DecK {
     const float* logits;
+    const float* obj;          // PACKED: dense objectness [frames][P] (the logits may then sit in host memory; only
+                               // the surviving rows are read from them)
     tk_b200_candidate_t* cands;
     uint32_t* counts;
     uint32_t P, C, L;          // proposals, classes, row length 5+C
@@ -116,7 +118,7 @@ __device__ __forceinline__ tk_b200_candidate_t decode_row(const DecK& k, const f
 
 // 4 CTAs per SM (<= 32 registers): with 3, only 48 of the 64 clusters of the bench batch are
 // co-resident (a cluster of 8 must sit in one GPC) and the launch needs two waves.
-template <int ACT>
+template <int ACT, bool PACKED>
 __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
     extern __shared__ __align__(16) uint8_t dsm[];
     uint32_t* flags = reinterpret_cast<uint32_t*>(dsm);            // [nwords] ballot bitmap
@@ -139,7 +141,10 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
 #pragma unroll
         for (int u = 0; u < kDecUnroll; ++u) {
             const uint32_t lr = base + u * kDecThreads + tid, r = row0 + lr;
-            obj[u] = (lr < k.rows_per_cta && r < k.P) ? ld_obj(fl + (size_t)r * k.L + 4) : __int_as_float(0x7fc00000);
+            if constexpr (PACKED)
+                obj[u] = (lr < k.rows_per_cta && r < k.P) ? __ldg(k.obj + (size_t)frame * k.P + r) : __int_as_float(0x7fc00000);
+            else
+                obj[u] = (lr < k.rows_per_cta && r < k.P) ? ld_obj(fl + (size_t)r * k.L + 4) : __int_as_float(0x7fc00000);
         }
 #pragma unroll
         for (int u = 0; u < kDecUnroll; ++u) {
@@ -242,7 +247,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
 
 template <int ACT>
 static tk_error_code_t launch_decode(const DecK& k, uint32_t frames, size_t smem, cudaStream_t stream) {
-    auto kern = decode_kernel<ACT>;
+    auto kern = k.obj ? decode_kernel<ACT, true> : decode_kernel<ACT, false>;
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     cudaLaunchConfig_t cfg{};
@@ -263,6 +268,10 @@ static tk_error_code_t launch_decode(const DecK& k, uint32_t frames, size_t smem
 using namespace tkb;
 
 extern "C" tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_params_t* p, cudaStream_t stream) {
+    return tkb::decode_detections_packed(p, nullptr, stream);
+}
+
+tk_error_code_t tkb::decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream) {
     if (!p || !p->d_logits || !p->d_counts || (!p->d_candidates && p->max_candidates)) return TK_ERROR_INVALID_ARGUMENT;
     if (p->num_frames == 0) return TK_SUCCESS;
     if (p->num_proposals == 0) return TK_ERROR_INVALID_DIMENSIONS;      // dims check of tk_object_detector.c:325-336
@@ -270,7 +279,7 @@ extern "C" tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_par
     const DeviceInfo* dev = device_info();
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
     DecK k{};
-    k.logits = p->d_logits; k.cands = p->d_candidates; k.counts = p->d_counts;
+    k.logits = p->d_logits; k.obj = d_objectness; k.cands = p->d_candidates; k.counts = p->d_counts;
     k.P = p->num_proposals; k.C = p->num_classes; k.L = 5 + p->num_classes;
     uint32_t per = (k.P + kDecCluster - 1) / kDecCluster;
     k.rows_per_cta = (per + 31) & ~31u;

@@ -16,6 +16,8 @@
 #include <stdlib.h>
 #include <string.h>
 #include <new>
+#include <thread>
+#include <vector>
 
 namespace tkb {
 
@@ -47,6 +49,8 @@ struct tk_b200_pipeline_s {
     uint32_t* d_counts;                                // [max_batch]
     tk_b200_candidate_t* d_dets;                       // [max_batch][max_detections]
     uint32_t* d_ndets;                                 // [max_batch]
+    float* h_obj;                                      // [max_batch][P] page-locked: objectness column packed on the host
+    float* d_obj;                                      // [max_batch][P]
     // Optional per-stage timing of process_device: 4 events per call (before pre,
     // after pre, after decode, after nms) on the caller's stream.
     int timing_on;
@@ -86,6 +90,8 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->d_counts) cudaFree(p->d_counts);
         if (p->d_dets) cudaFree(p->d_dets);
         if (p->d_ndets) cudaFree(p->d_ndets);
+        if (p->d_obj) cudaFree(p->d_obj);
+        if (p->h_obj) cudaFreeHost(p->h_obj);
         for (uint32_t i = 0; p->timing_ev && i < p->timing_cap * 4; ++i) if (p->timing_ev[i]) cudaEventDestroy(p->timing_ev[i]);
         free(p->timing_ev);
         if (p->s_up) cudaStreamDestroy(p->s_up);
@@ -175,7 +181,7 @@ extern "C" size_t tk_b200_pipeline_tensor_bytes(const tk_b200_pipeline_t* p) { r
 static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits, uint32_t n,
                                    void* d_tensor, tk_b200_candidate_t* d_cands, uint32_t* d_counts,
                                    tk_b200_candidate_t* d_dets, uint32_t* d_ndets, cudaStream_t st,
-                                   cudaEvent_t* tev = nullptr) {
+                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr) {
     const tk_b200_pipeline_config_t& c = p->cfg;
     tk_error_code_t rc;
     if (tev) cudaEventRecord(tev[0], st);
@@ -197,7 +203,7 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
         d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
         d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
         d.d_candidates = d_cands; d.d_counts = d_counts; d.max_candidates = c.max_candidates;
-        if ((rc = tk_kernels_decode_detections(&d, st)) != TK_SUCCESS) return rc;
+        if ((rc = decode_detections_packed(&d, d_obj, st)) != TK_SUCCESS) return rc;
         if (tev) cudaEventRecord(tev[2], st);
         tk_b200_nms_params_t m{};
         m.d_candidates = d_cands; m.d_counts = d_counts; m.num_frames = n; m.max_candidates = c.max_candidates;
@@ -309,20 +315,33 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
 
     // Whole-batch post-process when the logits are device-addressable where they lie.
     const float* logits_in_place = d_logits_all;
-    if (h_logits && !p->cfg.stage_host_logits) {
+    bool pack_objectness = false;
+    if (h_logits && p->cfg.stage_host_logits != 1) {
         cudaPointerAttributes at{};
-        if (cudaPointerGetAttributes(&at, h_logits) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+        if (cudaPointerGetAttributes(&at, h_logits) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
             logits_in_place = static_cast<const float*>(at.devicePointer);
-        else
+            pack_objectness = p->cfg.stage_host_logits == 0;
+        } else {
             cudaGetLastError();
-    }
-    if (logits_in_place) {
-        rc = run_kernels(p, nullptr, logits_in_place, n, nullptr, p->d_cands, p->d_counts, p->d_dets, p->d_ndets, p->s_post);
-        if (rc == TK_SUCCESS) {
-            TK_PIPE_TRY(cudaMemcpyAsync(h_dets, p->d_dets, (size_t)n * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_post));
-            TK_PIPE_TRY(cudaMemcpyAsync(h_ndets, p->d_ndets, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post));
         }
     }
+    if (pack_objectness && !p->h_obj) {
+        const size_t ob = (size_t)p->cfg.max_batch * p->cfg.num_proposals * sizeof(float);
+        if (cudaHostAlloc(reinterpret_cast<void**>(&p->h_obj), ob, cudaHostAllocDefault) != cudaSuccess ||
+            cudaMalloc(reinterpret_cast<void**>(&p->d_obj), ob) != cudaSuccess) {
+            tk_error_set_detail("pipeline objectness staging: %s", cudaGetErrorString(cudaGetLastError()));
+            return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
+        }
+    }
+    auto post_in_place = [&](const float* d_obj) -> tk_error_code_t {
+        tk_error_code_t r = run_kernels(p, nullptr, logits_in_place, n, nullptr, p->d_cands, p->d_counts, p->d_dets, p->d_ndets,
+                                        p->s_post, nullptr, d_obj);
+        if (r != TK_SUCCESS) return r;
+        TK_PIPE_TRY(cudaMemcpyAsync(h_dets, p->d_dets, (size_t)n * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_post));
+        TK_PIPE_TRY(cudaMemcpyAsync(h_ndets, p->d_ndets, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post));
+        return TK_SUCCESS;
+    };
+    if (logits_in_place && !pack_objectness) rc = post_in_place(nullptr);
     const bool chunk_logits = h_logits && !logits_in_place;
     const uint32_t chunks = (h_frames || chunk_logits) ? (n + p->chunk - 1) / p->chunk : 0;
     for (uint32_t k = 0; k < chunks && rc == TK_SUCCESS; ++k) {
@@ -357,6 +376,35 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
             TK_PIPE_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h_tensor) + (size_t)f0 * p->tensor_bytes,
                                         p->d_tensor + (size_t)f0 * p->tensor_bytes, (size_t)m * p->tensor_bytes,
                                         cudaMemcpyDeviceToHost, p->s_down));
+    }
+    if (pack_objectness && rc == TK_SUCCESS) {
+        // The frame copies are queued; while the copy engine works through them, host threads pack the objectness
+        // word of every row (4 bytes out of 340) into the page-locked column, which then crosses PCIe as one dense
+        // copy instead of one read request per row (profiles/r1_pcie_inplace.md).  Pure data movement: the
+        // threshold, like everything else, is applied by decode_kernel.
+        const size_t P = p->cfg.num_proposals, L = 5 + (size_t)p->cfg.num_classes;
+        const size_t rows = (size_t)n * P;
+        const unsigned hw = std::thread::hardware_concurrency();
+        const unsigned T = rows < 65536 ? 1u : (hw >= 16 ? 4u : (hw >= 4 ? 2u : 1u));
+        float* dst = p->h_obj;
+        auto work = [=](unsigned t) {
+            const size_t a = rows * t / T, b = rows * (t + 1) / T;
+            const float* sp = h_logits + a * L + 4;
+            for (size_t r = a; r < b; ++r, sp += L) dst[r] = *sp;
+        };
+        std::vector<std::thread> pool;
+        unsigned started = 1;                                // range 0 is the caller's
+        try {
+            for (; started < T; ++started) pool.emplace_back(work, started);
+        } catch (...) {
+        }
+        work(0);
+        for (unsigned t = started; t < T; ++t) work(t);      // ranges whose thread could not be started
+        for (auto& th : pool) th.join();
+        rc = [&]() -> tk_error_code_t {
+            TK_PIPE_TRY(cudaMemcpyAsync(p->d_obj, p->h_obj, rows * sizeof(float), cudaMemcpyHostToDevice, p->s_post));
+            return post_in_place(p->d_obj);
+        }();
     }
     // Drain even after an error so no copy is left in flight on the caller's buffers.
     cudaError_t es[4] = {cudaStreamSynchronize(p->s_up), cudaStreamSynchronize(p->s_compute),

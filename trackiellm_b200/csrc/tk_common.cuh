@@ -29,6 +29,11 @@ struct DeviceInfo {
 // Cached per-device properties; returns nullptr when no usable CUDA device.
 const DeviceInfo* device_info(int* out_device = nullptr);
 
+// decode.cu: tk_kernels_decode_detections with the objectness column supplied as a dense device array [frames][P]
+// (nullptr: read from the rows).  The pipeline's host-logits path packs that column on the host so the rows can stay in
+// page-locked host memory: pass 1 reads HBM, only the surviving rows cross PCIe.
+tk_error_code_t decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream);
+
 // Number of kernels this library has enqueued (every launcher goes through
 // launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
 void count_launch();

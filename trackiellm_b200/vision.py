@@ -361,7 +361,7 @@ class Pipeline:
                  mean=IMAGENET_MEAN, std=IMAGENET_STD, num_proposals: int = 25200, num_classes: int = 80,
                  act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
                  max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False,
-                 stage_host_logits: bool = False):
+                 stage_host_logits: int = 0):
         f16 = out_dtype == torch.float16
         if arith is None:
             arith = ARITH_HALF if f16 else ARITH_EXACT
