@@ -51,6 +51,23 @@ I420 = False
 SRC_NAME = "1080p RGB8"
 
 
+def frame_bytes_over_pcie() -> tuple[int, bool]:
+    """Bytes of one frame that cross PCIe in the host-buffer path, and whether the frames are read in place: sparse
+    geometries (y_ratio >= 2) with 16-byte rows are pulled row by row by the pre-process kernel, which only ever
+    stages the two source rows of each output row (src/vision/tk_image_preprocessor.c:49,51) — otherwise the whole
+    frame is copied.  Mirrors tkb::preprocess_reads_rows_sparsely (csrc/preprocess.cu)."""
+    row = SRC_W * (1 if I420 else 3)
+    y_ratio = np.float32(np.float32(SRC_H) - np.float32(1)) / np.float32(DST)
+    if y_ratio < 2 or row % 16 or (I420 and (SRC_W // 2) % 16):
+        return FRAME_BYTES, False
+    ys = np.minimum((y_ratio * np.arange(DST, dtype=np.float32)).astype(np.int64), SRC_H - 2)
+    luma = np.unique(np.concatenate([ys, ys + 1]))
+    total = len(luma) * row
+    if I420:
+        total += 2 * len(np.unique(np.minimum(luma >> 1, SRC_H // 2 - 1))) * (SRC_W // 2)
+    return int(total), True
+
+
 def set_workload(name: str) -> None:
     """Default = BASELINE.json configs[1]+[2] (the metric's configuration).  "4k-i420" = configs[3]: 4K planar
     YUV420 camera frames (src/ffi/c_api/tk_ffi_api.c:917-931) through the full pre + post pipeline."""
@@ -386,6 +403,7 @@ def run_b200(args) -> None:
                     "frac": d["frac"], "traffic": d["traffic"], "peak_source": peak_src,
                     "ms_per_launch": d["ms_per_launch"], "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
                     "share_of_step": d["ms_per_launch"] / max(sum(per_launch_ms), 1e-12)}
+        frame_pcie, frames_in_place = frame_bytes_over_pcie()
         step_ms = ms_total / K
         step_ach = (ALG_PRE + ALG_POST) * B / (step_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": "frames/s", "n_gpus": world,
@@ -397,13 +415,17 @@ def run_b200(args) -> None:
                 "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
                                   "unit": "GB/s", "frac": step_ach / peak},
                 "e2e": {"value": world * B * Ke / e2e_s, "unit": "frames/s",
-                        "h2d_bytes_per_step": B * (FRAME_BYTES + (LOGIT_BYTES, P * 4, 0)[(1, 0, 2).index(args.logits_mode)]),
-                        "host_bytes_read_in_place_per_step": (0 if args.logits_mode == 1 else
-                                                              int(np.sum(np.minimum(dev_cand_counts, 4096))) * (5 + NC) * 4
-                                                              + (B * P * 64 if args.logits_mode == 2 else 0)),
+                        "h2d_bytes_per_step": B * ((0 if frames_in_place else FRAME_BYTES)
+                                                   + (LOGIT_BYTES, P * 4, 0)[(1, 0, 2).index(args.logits_mode)]),
+                        "host_bytes_read_in_place_per_step": (B * frame_pcie if frames_in_place else 0) + (
+                            0 if args.logits_mode == 1 else int(np.sum(np.minimum(dev_cand_counts, 4096))) * (5 + NC) * 4
+                            + (B * P * 64 if args.logits_mode == 2 else 0)),
                         "d2h_bytes_per_step": B * (MAX_DET * 28 + 4), "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke,
                         "api": "tk_b200_pipeline_process_host (pinned host frames + logits in, host detections + counts out; "
-                               "the fp16 tensors stay on the device for the detector); frames are copied H2D in chunks, "
+                               "the fp16 tensors stay on the device for the detector); "
+                               + ("the pinned frames are read in place by the pre-process kernel's row ring (only the two source "
+                                  "rows of each output row cross PCIe: %d of %d bytes per frame), " % (frame_pcie, FRAME_BYTES)
+                                  if frames_in_place else "frames are copied H2D in chunks, ")
                                + {1: "logits are copied H2D in chunks",
                                   2: "the pinned logits are read in place over PCIe by decode_kernel (objectness word of every "
                                      "row, 64 B per request, + surviving rows), not copied",
@@ -411,7 +433,9 @@ def run_b200(args) -> None:
                                      "packed by 4 host threads while the frame copies run and uploaded as one dense array; "
                                      "decode_kernel reads only the surviving rows in place over PCIe"}[args.logits_mode]},
                 "e2e_device_logits": {"value": world * B * Ke / e2e_dl_s, "unit": "frames/s",
-                                      "h2d_bytes_per_step": B * FRAME_BYTES, "d2h_bytes_per_step": B * (MAX_DET * 28 + 4),
+                                      "h2d_bytes_per_step": 0 if frames_in_place else B * FRAME_BYTES,
+                                      "host_bytes_read_in_place_per_step": B * frame_pcie if frames_in_place else 0,
+                                      "d2h_bytes_per_step": B * (MAX_DET * 28 + 4),
                                       "api": "tk_b200_pipeline_process_host_frames (logits already in HBM)"},
                 "gpu_launches": launches, "clocks": clocks,
                 "detections_per_frame": float(np.mean(dev_counts))}

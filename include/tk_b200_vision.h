@@ -312,7 +312,11 @@ TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_device(
  * ordered by events.  Page-locked h_logits are not copied: the 4-byte objectness
  * word of each 340-byte row is packed into a dense column on the host (threads,
  * while the frame copies run) and uploaded, and decode reads only the surviving
- * rows in place over PCIe — 2 % of the tensor crosses the link.  h_logits may
+ * rows in place over PCIe — 2 % of the tensor crosses the link.  Page-locked
+ * h_frames whose geometry only samples two source rows per output row
+ * (height ratio >= 2, e.g. 4K -> 640) and whose rows are multiples of 16 bytes
+ * are not copied either: the pre-process kernel's row ring fetches exactly
+ * those rows in place (4K I420: 8.6 of 12.4 MB per frame cross the link).  h_logits may
  * be NULL (pre-process only) and h_frames may be NULL (post-process only).  The model-input tensors stay on the device for
  * the detector (tk_b200_pipeline_tensor_device_ptr) and are also downloaded when
  * h_tensor != NULL.  Blocks until the outputs are in host memory. */

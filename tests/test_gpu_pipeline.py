@@ -43,6 +43,35 @@ def check_dets(dets, counts, logits, restore=None):
         assert got.tobytes() == ref.tobytes(), f"frame {i}: {len(got)} vs {len(ref)} detections"
 
 
+@pytest.mark.parametrize("w,h,fmt", [(320, 240, "rgb"), (250, 240, "rgb"), (100, 60, "rgb"), (320, 240, "i420"), (320, 240, "rgba")])
+def test_process_host_frame_paths_bitexact(w, h, fmt):
+    """Page-locked frames: sparse geometries with 16-byte rows are read IN PLACE over PCIe by the row ring, the others
+    (row bytes not a multiple of 16, dense geometry) are copied in chunks — every path bit-exact, twice per handle."""
+    n = 5
+    rng = np.random.default_rng(w + h)
+    if fmt == "i420":
+        bufs = np.stack([synth.i420_frame(w, h, 40 + i) for i in range(n)])
+        rgb = [O.i420_to_rgb8(b, w, h) for b in bufs]
+        kw = dict(fmt=V.PIXEL_I420)
+    elif fmt == "rgba":
+        rgb = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(n)]
+        bufs = np.stack([np.concatenate([r, rng.integers(0, 256, (h, w, 1), dtype=np.uint8)], axis=2) for r in rgb]).reshape(n, -1)
+        kw = dict(fmt=V.PIXEL_RGBA8)
+    else:
+        rgb = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(n)]
+        bufs = np.stack(rgb).reshape(n, -1)
+        kw = dict(fmt=V.PIXEL_RGB8)
+    with make_pipe(n, width=w, height=h, chunk_frames=2, arith=V.ARITH_EXACT, **kw) as pipe:
+        hf = torch.from_numpy(bufs).pin_memory()
+        ht = torch.empty((n, 3, 48, 64), dtype=torch.float32).pin_memory()
+        for _ in range(2):
+            ht.zero_()
+            pipe.process_host(hf, None, None, None, tensor=ht)
+            for i in range(n):
+                ref = O.preprocess_rgb8(rgb[i], 64, 48)
+                assert np.array_equal(ht[i].numpy().view(np.uint32), ref.view(np.uint32)), (i, w, h, fmt)
+
+
 def test_process_device_vs_oracle():
     n = 7
     frames, logits = inputs(n)

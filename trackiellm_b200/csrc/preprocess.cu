@@ -578,6 +578,27 @@ static tk_error_code_t launch_type(const PreK& k, bool f16, int ar, bool lbox, b
 
 using namespace tkb;
 
+// True when a launch with these parameters (a) stages only the two source rows of each output row (y_ratio >= 2, so
+// a large part of every frame is never fetched) and (b) moves rows with 16-byte bulk copies that end exactly at the
+// row's last byte — the conditions under which the pipeline lets the kernel read page-locked HOST frames in place
+// over PCIe instead of copying them to HBM first.
+bool tkb::preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t* prm) {
+    if (!prm || prm->d_input_ptrs || prm->output_height == 0 || prm->output_width == 0) return false;
+    const uint32_t fmt = prm->input_format == TK_PIXEL_FORMAT_RGBA8 ? FMT_RGBA8 : (prm->input_format == TK_PIXEL_FORMAT_I420 ? FMT_I420 : FMT_RGB8);
+    const uint32_t bpp = fmt == FMT_RGB8 ? 3 : (fmt == FMT_RGBA8 ? 4 : 1);
+    const unsigned long long row_bytes = (unsigned long long)prm->input_width * bpp;
+    const unsigned long long stride = prm->input_stride_bytes ? prm->input_stride_bytes : row_bytes;
+    if (row_bytes % 16 || stride % 16 || reinterpret_cast<uintptr_t>(prm->d_input) % 16) return false;
+    if (fmt == FMT_I420 && ((prm->input_width / 2) % 16 || (stride / 2) % 16 || (stride * prm->input_height) % 16 ||
+                            ((stride / 2) * (prm->input_height / 2)) % 16))
+        return false;
+    if (prm->input_frame_pitch_bytes % 16) return false;
+    uint32_t new_w = prm->output_width, new_h = prm->output_height, pl = 0, pt = 0;
+    if (prm->resize_mode == TK_B200_RESIZE_LETTERBOX)
+        letterbox_geometry(prm->input_width, prm->input_height, prm->output_width, prm->output_height, &new_w, &new_h, &pl, &pt);
+    return ((float)prm->input_height - 1.0f) / (float)new_h >= 2.0f;
+}
+
 extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_batch_params_t* prm, cudaStream_t stream) {
     if (!prm || (!prm->d_input && !prm->d_input_ptrs) || !prm->d_output) return TK_ERROR_INVALID_ARGUMENT;
     if (prm->num_frames == 0) return TK_SUCCESS;

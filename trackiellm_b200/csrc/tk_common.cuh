@@ -29,6 +29,9 @@ struct DeviceInfo {
 // Cached per-device properties; returns nullptr when no usable CUDA device.
 const DeviceInfo* device_info(int* out_device = nullptr);
 
+// preprocess.cu: see the definition.
+bool preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t* prm);
+
 // decode.cu: tk_kernels_decode_detections with the objectness column supplied as a dense device array [frames][P]
 // (nullptr: read from the rows).  The pipeline's host-logits path packs that column on the host so the rows can stay in
 // page-locked host memory: pass 1 reads HBM, only the surviving rows cross PCIe.
