@@ -289,7 +289,7 @@ typedef struct {
     int                   stage_host_logits;  /* process_host with page-locked host logits (pageable logits are always
                                                  staged): 0 = the rows stay in host memory — their objectness column
                                                  is packed by host threads and copied as one dense array, decode reads
-                                                 only the surviving rows over PCIe; 1 = copy the whole tensor to HBM
+                                                 only the surviving rows over PCIe (batches under 65536 rows behave as 2); 1 = copy the whole tensor to HBM
                                                  first; 2 = decode reads objectness words and surviving rows in place
                                                  over PCIe (one read request per row)                              */
 } tk_b200_pipeline_config_t;

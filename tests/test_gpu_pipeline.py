@@ -72,6 +72,21 @@ def test_process_host_frame_paths_bitexact(w, h, fmt):
                 assert np.array_equal(ht[i].numpy().view(np.uint32), ref.view(np.uint32)), (i, w, h, fmt)
 
 
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_process_host_logits_modes_full_head(mode):
+    """25200-row heads (>= 65536 rows per batch: mode 0 packs the objectness column with host threads and decode reads
+    only the surviving rows in place), every mode against the oracle; post-process only (no frames)."""
+    n = 4
+    logits = np.stack([synth.logits_tensor(70 + i, adversarial=(i == 1)) for i in range(n)])
+    with make_pipe(n, num_proposals=synth.NUM_PROPOSALS, stage_host_logits=mode) as pipe:
+        _, hd, hc = pipe.alloc_outputs(n, pinned=True)
+        hl = torch.from_numpy(logits).pin_memory()
+        for _ in range(2):
+            hd.zero_(); hc.zero_()
+            pipe.process_host(None, hl, hd, hc)
+            check_dets(hd, hc, logits)
+
+
 def test_process_device_vs_oracle():
     n = 7
     frames, logits = inputs(n)

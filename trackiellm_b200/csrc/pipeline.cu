@@ -326,7 +326,8 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
         cudaPointerAttributes at{};
         if (cudaPointerGetAttributes(&at, h_logits) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
             logits_in_place = static_cast<const float*>(at.devicePointer);
-            pack_objectness = p->cfg.stage_host_logits == 0;
+            // a frame or two: one read request per row over PCIe (~42 us per 25200 rows) beats a single-threaded gather
+            pack_objectness = p->cfg.stage_host_logits == 0 && (size_t)n * p->cfg.num_proposals >= 65536;
         } else {
             cudaGetLastError();
         }
@@ -417,7 +418,7 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
         const size_t P = p->cfg.num_proposals, L = 5 + (size_t)p->cfg.num_classes;
         const size_t rows = (size_t)n * P;
         const unsigned hw = std::thread::hardware_concurrency();
-        const unsigned T = rows < 65536 ? 1u : (hw >= 16 ? 4u : (hw >= 4 ? 2u : 1u));
+        const unsigned T = hw >= 16 ? 4u : (hw >= 4 ? 2u : 1u);
         float* dst = p->h_obj;
         auto work = [=](unsigned t) {
             const size_t a = rows * t / T, b = rows * (t + 1) / T;
