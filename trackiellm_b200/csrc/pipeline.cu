@@ -299,11 +299,17 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
 //
 // Logits: decode needs 4 bytes of every 340-byte row (the objectness word) and the
 // full row only for the few hundred survivors, so copying the tensor to HBM first
-// moves ~10x more bytes over PCIe than the kernel reads.  When the caller's logits
+// moves ~50x more bytes over PCIe than the kernel needs.  When the caller's logits
 // are in page-locked host memory (tk_b200_host_alloc / cudaHostAlloc: device-
-// addressable under UVA) decode_kernel reads them IN PLACE over PCIe: one launch
-// for the whole batch on its own stream, concurrent with the frame uploads.
-// Pageable logits (or stage_host_logits = 1) are staged through HBM chunk by chunk.
+// addressable under UVA) they stay there: the objectness column is packed into a
+// dense page-locked array by host threads while the frame copies run, uploaded as
+// one copy, and decode_kernel<PACKED> reads only the surviving rows in place over
+// PCIe (stage_host_logits = 2 or a batch of a frame or two: the objectness words are
+// read in place as well, one PCIe request per row).  One launch for the whole batch
+// on its own stream, concurrent with the frame uploads.  Pageable logits (or
+// stage_host_logits = 1) are staged through HBM chunk by chunk.
+//
+// Frames of a sparse geometry are not copied either (see frames_in_place below).
 static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_frames, const float* h_logits,
                                          const float* d_logits_all, uint32_t n, void* h_tensor,
                                          tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
@@ -332,10 +338,10 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
             cudaGetLastError();
         }
     }
-    if (pack_objectness && !p->h_obj) {
+    if (pack_objectness && (!p->h_obj || !p->d_obj)) {
         const size_t ob = (size_t)p->cfg.max_batch * p->cfg.num_proposals * sizeof(float);
-        if (cudaHostAlloc(reinterpret_cast<void**>(&p->h_obj), ob, cudaHostAllocDefault) != cudaSuccess ||
-            cudaMalloc(reinterpret_cast<void**>(&p->d_obj), ob) != cudaSuccess) {
+        if ((!p->h_obj && cudaHostAlloc(reinterpret_cast<void**>(&p->h_obj), ob, cudaHostAllocDefault) != cudaSuccess) ||
+            (!p->d_obj && cudaMalloc(reinterpret_cast<void**>(&p->d_obj), ob) != cudaSuccess)) {
             tk_error_set_detail("pipeline objectness staging: %s", cudaGetErrorString(cudaGetLastError()));
             return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
         }
