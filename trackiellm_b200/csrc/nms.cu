@@ -209,39 +209,113 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame) {
     // with R same-class predecessors, bit r of segmask[t] <=> the predecessor of
     // segment rank r has IoU > thr with it.  Segments longer than 64 (crowds of one
     // class, class-agnostic mode) take the blocked path below instead.
-    for (uint32_t t = tid; t < K; t += kNmsThreads) {
-        const unsigned long long kt = keys2[t];
-        const uint32_t c = (uint32_t)(kt >> 32);
-        const int4 me = box[(uint32_t)kt];
-        unsigned long long mdist = 0;                              // bit d-1: predecessor at distance d
-        uint32_t R = 0;
-        for (uint32_t j = t; j-- > 0;) {
-            const unsigned long long kj = keys2[j];
-            if ((uint32_t)(kj >> 32) != c) break;
-            if (R == 63) { seg_overflow = 1; break; }           // a segment longer than 64
-            if (iou_rect(box[(uint32_t)kj], me) > k.thr) mdist |= 1ull << R;
-            ++R;
+    //
+    // The (candidate, predecessor) pairs are dealt out evenly: a frame's time is set by its
+    // longest class (60 candidates of one class = 59 dependent IoUs for the last of them when
+    // every candidate walks its own predecessors), while the pair list of a 480-candidate frame is
+    // ~14 pairs per thread.  wpre[t] = number of pairs before candidate t (exclusive prefix of R).
+    uint32_t* wpre = reinterpret_cast<uint32_t*>(keys);            // [K + 1]; the score keys are no longer needed
+    {
+        uint32_t carry_start = 0, carry_sum = 0;
+        for (uint32_t base = 0; base < K; base += kNmsThreads) {
+            const uint32_t t = base + tid;
+            const bool valid = t < K;
+            const uint32_t c = valid ? (uint32_t)(keys2[t] >> 32) : 0u;
+            const bool head = valid && (t == 0 || (uint32_t)(keys2[t - 1] >> 32) != c);
+            uint32_t start = head ? t : 0u;                        // inclusive max-scan: start of my segment
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, start, d);
+                if ((int)lane >= d) start = max(start, o);
+            }
+            if (lane == 31) warp_tot[warp] = start;
+            __syncthreads();
+            uint32_t prev = carry_start, all = carry_start;
+#pragma unroll
+            for (int w = 0; w < kNmsWarps; ++w) { const uint32_t v = warp_tot[w]; if ((uint32_t)w < warp) prev = max(prev, v); all = max(all, v); }
+            start = max(start, prev);
+            const uint32_t R = valid ? t - start : 0u;
+            if (R >= 64) seg_overflow = 1;                         // a segment longer than 64
+            uint32_t inc = R;                                      // inclusive sum-scan of R
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+                if ((int)lane >= d) inc += o;
+            }
+            __syncthreads();                                       // warp_tot: everyone has read the segment starts
+            if (lane == 31) warp_tot[warp] = inc;
+            __syncthreads();
+            uint32_t before = carry_sum, tot = 0;
+#pragma unroll
+            for (int w = 0; w < kNmsWarps; ++w) { const uint32_t v = warp_tot[w]; before += (uint32_t)w < warp ? v : 0u; tot += v; }
+            if (valid) {
+                wpre[t] = before + inc - R;
+                segmask[t] = 0ull;
+                dead[t] = (uint8_t)(R == 0);                       // (fast path only) 1 = head of a segment
+            }
+            carry_start = all; carry_sum += tot;
+            __syncthreads();
         }
-        // distance d = 1..R maps to segment rank R - d
-        segmask[t] = R ? (__brevll(mdist) >> (64 - R)) : 0ull;
-        dead[t] = (uint8_t)(R == 0);                               // (fast path only) 1 = head of a segment
+        if (tid == 0) wpre[K] = carry_sum;
     }
     __syncthreads();
 
     uint32_t run = 0;
     if (!seg_overflow) {
-        // ---- B. each segment head resolves its segment sequentially (<= 64 steps) ----
+        const uint32_t total = wpre[K];
+        const uint32_t per = (total + kNmsThreads - 1) / kNmsThreads;
+        uint32_t pi = tid * per;
+        const uint32_t pend = min(pi + per, total);
+        if (pi < pend) {
+            uint32_t lo = 0, hi = K - 1;                           // last t with wpre[t] <= pi: the candidate owning pair pi
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi + 1) >> 1;
+                if (wpre[mid] <= pi) lo = mid; else hi = mid - 1;
+            }
+            uint32_t t = lo, w0 = wpre[t], R = wpre[t + 1] - w0, r = pi - w0;
+            int4 me = box[(uint32_t)keys2[t]];
+            unsigned long long m = 0;
+            for (; pi < pend; ++pi) {
+                if (iou_rect(box[(uint32_t)keys2[t - R + r]], me) > k.thr) m |= 1ull << r;
+                if (++r == R) {
+                    if (m) atomicOr(&segmask[t], m);
+                    m = 0; r = 0;
+                    if (pi + 1 < pend) {
+                        do { ++t; R = wpre[t + 1] - wpre[t]; } while (R == 0);     // pairs remain, so a later candidate has some
+                        me = box[(uint32_t)keys2[t]];
+                    }
+                }
+            }
+            if (m) atomicOr(&segmask[t], m);
+        }
+        __syncthreads();
+        // ---- B. each segment head resolves its segment sequentially (<= 64 steps).  Keys and masks
+        //         come in groups of four independent loads, so the chain per element is the kept-mask
+        //         update alone, not a shared-memory round trip ----
         for (uint32_t t = tid; t < K; t += kNmsThreads) {
             if (!dead[t]) continue;
             const uint32_t c = (uint32_t)(keys2[t] >> 32);
             unsigned long long kept = 0;
-            for (uint32_t r = 0; t + r < K; ++r) {
-                const unsigned long long kr = keys2[t + r];
-                if ((uint32_t)(kr >> 32) != c) break;
-                if ((segmask[t + r] & kept) == 0) {
-                    kept |= 1ull << r;
-                    const uint32_t i = (uint32_t)kr;                // score rank
-                    atomicOr(&keptbits[i >> 6], 1ull << (i & 63));
+            bool open = true;
+            for (uint32_t r0 = 0; open; r0 += 4) {
+                unsigned long long kq[4], sq[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t e = t + r0 + u;
+                    const bool in = e < K;
+                    kq[u] = in ? keys2[e] : 0ull;
+                    sq[u] = in ? segmask[e] : 0ull;
+                    if (!in) kq[u] = ~((unsigned long long)c << 32);   // a different class: ends the segment
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (!open) break;
+                    if ((uint32_t)(kq[u] >> 32) != c) { open = false; break; }
+                    if ((sq[u] & kept) == 0) {
+                        kept |= 1ull << (r0 + u);
+                        const uint32_t i = (uint32_t)kq[u];         // score rank
+                        atomicOr(&keptbits[i >> 6], 1ull << (i & 63));
+                    }
                 }
             }
         }
