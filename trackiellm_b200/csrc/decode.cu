@@ -67,19 +67,34 @@ __device__ __forceinline__ float ld_obj(const float* p) {
 static constexpr uint32_t kDecStage = 256;     // candidate records a CTA stages in shared memory (7 KB)
 static constexpr int kDecUnroll = 8;           // objectness loads in flight per thread
 
+// One row's worth of loads: up to 128 class logits (lane + 32u) and the 5-word head (lanes 0..4: cx, cy, w, h,
+// objectness), issued together — one memory round trip per row instead of one per 32 classes.  (Deeper prefetch —
+// the next row's loads in flight, or four rows staged with cp.async — measured no faster: with 64 warps per SM in pass 2
+// at once the pass is bound by instruction issue, not by the loads.)
+struct RowRegs { float v4[4]; float head; };
+__device__ __forceinline__ void load_row(const DecK& k, const float* row, uint32_t lane, RowRegs& q) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) q.v4[u] = (lane + 32u * u < k.C) ? __ldg(row + 5 + lane + 32u * u) : 0.0f;
+    q.head = lane < 5 ? __ldg(row + lane) : 0.0f;
+}
+
 template <int ACT>
-__device__ __forceinline__ tk_b200_candidate_t decode_row(const DecK& k, const float* row, uint32_t r, uint32_t lane, float* my_e) {
+__device__ __forceinline__ tk_b200_candidate_t decode_row(const DecK& k, const float* row, uint32_t r, uint32_t lane, float* my_e,
+                                                          const RowRegs& q) {
     // First-max class over raw logits: the reference's sequential scan
     //   best = 0; for j >= 1: if (v[j] > v[best]) best = j;      (tie rule of tk_attribute_classifier.c:83-88)
     // as two warp reductions on order-preserving integer keys.  -0 and +0 compare equal
     // (canonicalised by + 0.0f), a NaN at j >= 1 never wins (key 0, below every number),
     // a NaN at j == 0 is never displaced (key 0xffffffff); ties -> lowest index.
     uint32_t lk = 0, li = kNone; float lv = 0.0f;
-    for (uint32_t j = lane; j < k.C; j += 32) {
-        const float v = __ldg(row + 5 + j);
+    auto consider = [&](uint32_t j, float v) {
         const uint32_t key = (v != v) ? (j == 0 ? 0xffffffffu : 0u) : tk_dm_float_order_key(__fadd_rn(v, 0.0f));
         if (li == kNone || key > lk) { lk = key; li = j; lv = v; }
-    }
+    };
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+        if (lane + 32u * u < k.C) consider(lane + 32u * u, q.v4[u]);
+    for (uint32_t j = lane + 128; j < k.C; j += 32) consider(j, __ldg(row + 5 + j));
     const uint32_t mk = __reduce_max_sync(0xffffffffu, lk);
     const uint32_t bidx = __reduce_min_sync(0xffffffffu, (li != kNone && lk == mk) ? li : kNone);
     const uint32_t best = (bidx == kNone) ? 0u : bidx;
@@ -101,11 +116,9 @@ __device__ __forceinline__ tk_b200_candidate_t decode_row(const DecK& k, const f
         __syncwarp();
     }
     tk_b200_candidate_t c;
-    // lanes 0..4 hold cx, cy, w, h, objectness
-    const float head = lane < 5 ? __ldg(row + lane) : 0.0f;
-    const float cx = __shfl_sync(0xffffffffu, head, 0), cy = __shfl_sync(0xffffffffu, head, 1);
-    const float bw = __shfl_sync(0xffffffffu, head, 2), bh = __shfl_sync(0xffffffffu, head, 3);
-    const float obj = act_fn<ACT>(__shfl_sync(0xffffffffu, head, 4));
+    const float cx = __shfl_sync(0xffffffffu, q.head, 0), cy = __shfl_sync(0xffffffffu, q.head, 1);
+    const float bw = __shfl_sync(0xffffffffu, q.head, 2), bh = __shfl_sync(0xffffffffu, q.head, 3);
+    const float obj = act_fn<ACT>(__shfl_sync(0xffffffffu, q.head, 4));
     c.index = (int32_t)r;
     c.bbox.x = __float2int_rz(__fsub_rn(cx, __fmul_rn(bw, 0.5f)));   // :347  (int)(cx - w/2)
     c.bbox.y = __float2int_rz(__fsub_rn(cy, __fmul_rn(bh, 0.5f)));   // :348
@@ -187,24 +200,34 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 
     // ---- pass 2: one warp per surviving row, records staged in shared memory in row order ----
-    // Survivor s of this CTA goes to warp s mod 16 (balanced however the survivors cluster);
-    // its row is found by binary search in the word prefix + select inside the word.
+    // Survivor s of this CTA goes to warp s mod 16 (balanced however the survivors cluster).  Its row number is
+    // expanded from the bitmap once, thread per bit, into the first word of its record slot (where the index goes
+    // anyway): pass 2 is issue-bound with 64 warps per SM in it at once, and a per-row binary search + select-nth-bit
+    // by all 32 lanes cost more instructions than decoding the row.
     float* my_e = ebuf + (size_t)warp * k.C;
     const uint32_t local_n = __popc(flags[k.nwords - 1]) + wpre[k.nwords - 1];
-    for (uint32_t sidx = warp; sidx < min(local_n, kDecStage); sidx += kDecWarps) {
-        uint32_t lo = 0, hi = k.nwords - 1;                        // last word with wpre[w] <= sidx
-        while (lo < hi) {
-            const uint32_t mid = (lo + hi + 1) >> 1;
-            if (wpre[mid] <= sidx) lo = mid; else hi = mid - 1;
+    const uint32_t lim = min(local_n, kDecStage);
+    for (uint32_t i = tid; i < k.nwords * 32; i += kDecThreads) {
+        const uint32_t word = flags[i >> 5], b = i & 31;
+        if ((word >> b) & 1u) {
+            const uint32_t lpos = wpre[i >> 5] + __popc(word & ((1u << b) - 1u));
+            if (lpos < kDecStage) stage[lpos * 7] = row0 + i;
         }
-        const uint32_t b = __fns(flags[lo], 0, (int)(sidx - wpre[lo]) + 1);
-        const uint32_t r = row0 + lo * 32 + b;
-        const tk_b200_candidate_t c = decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e);
+    }
+    __syncthreads();
+    auto row_of = [&](uint32_t sidx) -> uint32_t { return stage[sidx * 7]; };
+    auto put = [&](uint32_t sidx, const tk_b200_candidate_t& c) {
         if (lane == 0) {
             uint32_t* sp = stage + sidx * 7;
             sp[0] = (uint32_t)c.index; sp[1] = (uint32_t)c.bbox.x; sp[2] = (uint32_t)c.bbox.y; sp[3] = (uint32_t)c.bbox.w;
             sp[4] = (uint32_t)c.bbox.h; sp[5] = __float_as_uint(c.confidence); sp[6] = c.class_id;
         }
+    };
+    for (uint32_t sidx = warp; sidx < lim; sidx += kDecWarps) {
+        const uint32_t r = row_of(sidx);
+        RowRegs q;
+        load_row(k, fl + (size_t)r * k.L, lane, q);
+        put(sidx, decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e, q));
     }
     __syncthreads();
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -238,7 +261,9 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
                 const uint32_t pos = frame_pre + lpos;
                 if (pos >= k.cap) { bits = 0; break; }             // later rows only have larger pos
                 const uint32_t r = row0 + w * 32 + b;
-                const tk_b200_candidate_t c = decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e);
+                RowRegs q;
+                load_row(k, fl + (size_t)r * k.L, lane, q);
+                const tk_b200_candidate_t c = decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e, q);
                 if (lane == 0) out[pos] = c;
             }
         }
