@@ -163,11 +163,15 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
         for (int u = 0; u < kDecUnroll; ++u) {
             const uint32_t lr = base + u * kDecThreads + tid;
             const bool pass = act_fn<ACT>(obj[u]) > k.thr;         // NaN never passes
-            if (pass) {
-                // pull the surviving row towards L2 now; pass 2 reads it a few microseconds later
-                const char* rp = reinterpret_cast<const char*>(fl + (size_t)(row0 + lr) * k.L);
-                const uint32_t rb = k.L * 4;
-                for (uint32_t o = 0; o < rb; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + o));
+            if constexpr (PACKED) {
+                // the rows are in host memory: start pulling a surviving row over PCIe now, pass 2 reads it a few
+                // microseconds later.  (For rows in HBM the prefetch buys nothing now that pass 2 issues a row's loads
+                // together: 0.5 - 1 us per 64 frames FASTER without it.)
+                if (pass) {
+                    const char* rp = reinterpret_cast<const char*>(fl + (size_t)(row0 + lr) * k.L);
+                    const uint32_t rb = k.L * 4;
+                    for (uint32_t o = 0; o < rb; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + o));
+                }
             }
             const uint32_t b = __ballot_sync(0xffffffffu, pass);
             if (lane == 0 && lr < k.rows_per_cta) flags[lr >> 5] = b;
