@@ -1,7 +1,8 @@
 """Experiment: step time of the bench workload with NO stage events between the kernels (151.0 us per 64-frame step
 on B200 against 163 us with the four event records per step), and a checksum of tensor + detections + counts.
 It was also the A/B harness for decode launched as a programmatic dependent of the pre-process kernel (a library
-build that read TK_B200_PDL; 157.8 us, same checksum, dropped - DESIGN 9.1); the variable is ignored now."""
+build that read TK_B200_PDL; 157.8 us, same checksum, dropped - DESIGN 9.1); the variable is ignored now.
+TK_B200_PDL_PRE=0 turns off the pre-process kernel's early launch behind the previous step's NMS (150.9 vs 147.6 us)."""
 import os, sys, zlib, torch
 sys.path.insert(0, ".")
 import bench as Bn
@@ -24,4 +25,4 @@ for _ in range(5):
     e1.record(); torch.cuda.synchronize()
     best = min(best, e0.elapsed_time(e1) * 5)
 crc = zlib.crc32(d_dets.cpu().numpy().tobytes() + d_counts.cpu().numpy().tobytes() + d_tensor.cpu().numpy().tobytes())
-print(f"PDL={os.environ.get('TK_B200_PDL', '0')}: {best:.1f} us/step crc={crc:08x}", flush=True)
+print(f"PDL_PRE={os.environ.get('TK_B200_PDL_PRE', '1')}: {best:.1f} us/step crc={crc:08x}", flush=True)

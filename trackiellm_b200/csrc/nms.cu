@@ -428,6 +428,9 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame) {
 
 // One CTA per frame while the batch fits one wave; larger batches loop (every exit of nms_frame is CTA-uniform).
 __global__ void __launch_bounds__(kNmsThreads, 3) nms_kernel(const NmsK k) {
+    // Nothing this grid reads is written by the kernel the pipeline launches next (the pre-process kernel of the
+    // following step, which ends on griddepcontrol.wait): let it start on the SMs this grid does not fill.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     for (uint32_t frame = blockIdx.x; frame < k.num_frames; frame += gridDim.x) {
         nms_frame(k, frame);
         __syncthreads();
