@@ -9,16 +9,26 @@ decode + class-wise NMS of 64 detector-head tensors of 25200x85 fp32, configs[2]
 Frames shard by frame across ranks with no collective: weak scaling, every rank
 owns its own 64-frame batch; torch.distributed (gloo) is used only for the barrier and the max.
 
-  value     whole-job frames/s with inputs resident in HBM, CUDA-event timed, max over ranks
-  e2e       the same metric through tk_b200_pipeline_process_host: pinned HOST frames + logits in,
-            HOST detections out, every host<->device copy inside the timed region
-  roofline  the dominant kernel's algorithmic bytes / its CUDA-event time vs the measured HBM peak
-  cpu_baseline / --impl reference
-            the reference's own CPU pre-processor (oracle/_ref/libtkref.so, compiled from
-            /root/reference/src/vision/tk_image_preprocessor.c) + the CPU restatement of
-            decode/NMS (the reference's postprocess is a stub) on all host cores
+ONE invocation prints ONE JSON line that carries, beside the contract's keys:
 
-The oracle is imported only by cpu_baseline() / the reference arm.
+  value / roofline   the headline in the REFERENCE's arithmetic: every fp32 operation of
+                     src/vision/tk_image_preprocessor.c:63-66,84-98 in its order, rounded RNE to fp16
+                     (bit-exact to RNE(oracle)); inputs resident in HBM, CUDA-event timed, max over ranks
+  half               the same workload with the half2-lerp arithmetic (within the 1e-2 fp16 bar, not bit-exact)
+  e2e                the same metric through tk_b200_pipeline_process_host: pinned HOST frames + logits in,
+                     HOST detections out (the tensors stay on the device for the detector)
+  e2e_with_tensor    the same call with h_tensor set: the fp16 tensors also come back to the host
+  e2e_link_ceiling   raw pinned host->device copy rate measured in this run, as frames/s of this workload
+  workloads.4k-i420  BASELINE configs[3] per GPU: 32 frames 3840x2160 I420 through pre + decode + NMS
+  sweep              BASELINE configs[4]: global batch 1 .. 1024 sharded over the ranks (device-resident and e2e,
+                     CPU arm beside it at N = 1)
+  detect_latency_us  configs[0]: one 640x480 HOST frame through tk_object_detector_detect
+  cpu_baseline / --impl reference
+                     the reference's own CPU pre-processor (oracle/_ref/libtkref.so, compiled from
+                     /root/reference/src/vision/tk_image_preprocessor.c) + the CPU restatement of
+                     decode/NMS (the reference's postprocess is a stub) on all host cores
+
+The oracle is imported only by cpu_baseline() / cpu_sweep() / the reference arm.
 """
 from __future__ import annotations
 
@@ -26,9 +36,11 @@ import argparse
 import ctypes as C
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
+from dataclasses import dataclass
 
 import numpy as np
 
@@ -36,62 +48,83 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-METRIC = "frames/s (pre+decode+NMS, 1080p->640^2)"
-SRC_W, SRC_H = 1920, 1080
 DST = 640
 P, NC = 25200, 80
-FRAME_BYTES = SRC_W * SRC_H * 3
 TENSOR_BYTES_F16 = DST * DST * 3 * 2
 LOGIT_BYTES = P * (5 + NC) * 4
-# every source byte once + every output byte once; decode+NMS: every logit byte once.
-ALG_PRE = FRAME_BYTES + TENSOR_BYTES_F16          # 8 678 400 B / frame
-ALG_POST = LOGIT_BYTES                            # 8 568 000 B / frame
 CONF_THR, IOU_THR, MAX_DET = 0.5, 0.5, 500        # tests/tk_vision_full_test.c:67, tk_vision_pipeline.c:376-377
-I420 = False
-SRC_NAME = "1080p RGB8"
+DET_BYTES = MAX_DET * 28 + 4
 
 
-def frame_bytes_over_pcie() -> tuple[int, bool]:
-    """Bytes of one frame that cross PCIe in the host-buffer path, and whether the frames are read in place: sparse
-    geometries (y_ratio >= 2) with 16-byte rows are pulled row by row by the pre-process kernel, which only ever
-    stages the two source rows of each output row (src/vision/tk_image_preprocessor.c:49,51) — otherwise the whole
-    frame is copied.  Mirrors tkb::preprocess_reads_rows_sparsely (csrc/preprocess.cu)."""
-    row = SRC_W * (1 if I420 else 3)
-    y_ratio = np.float32(np.float32(SRC_H) - np.float32(1)) / np.float32(DST)
-    if y_ratio < 2 or row % 16 or (I420 and (SRC_W // 2) % 16):
-        return FRAME_BYTES, False
-    ys = np.minimum((y_ratio * np.arange(DST, dtype=np.float32)).astype(np.int64), SRC_H - 2)
-    luma = np.unique(np.concatenate([ys, ys + 1]))
-    total = len(luma) * row
-    if I420:
-        total += 2 * len(np.unique(np.minimum(luma >> 1, SRC_H // 2 - 1))) * (SRC_W // 2)
-    return int(total), True
+@dataclass
+class Workload:
+    key: str
+    src_w: int
+    src_h: int
+    i420: bool
+    src_name: str
+    default_batch: int
+
+    @property
+    def frame_bytes(self) -> int:
+        return self.src_w * self.src_h * 3 // 2 if self.i420 else self.src_w * self.src_h * 3
+
+    @property
+    def alg_pre(self) -> int:
+        """every source byte once + every output byte once."""
+        return self.frame_bytes + TENSOR_BYTES_F16
+
+    @property
+    def metric(self) -> str:
+        return "frames/s (pre+decode+NMS, 4K I420->640^2)" if self.i420 else "frames/s (pre+decode+NMS, 1080p->640^2)"
+
+    def frame_bytes_over_pcie(self) -> tuple[int, bool]:
+        """Bytes of one frame that cross PCIe in the host-buffer path, and whether the frames are read in place: sparse
+        geometries (y_ratio >= 2) with 16-byte rows are pulled row by row by the pre-process kernel, which only ever
+        stages the two source rows of each output row (src/vision/tk_image_preprocessor.c:49,51) — otherwise the whole
+        frame is copied.  Mirrors tkb::preprocess_reads_rows_sparsely (csrc/preprocess.cu)."""
+        row = self.src_w * (1 if self.i420 else 3)
+        y_ratio = np.float32(np.float32(self.src_h) - np.float32(1)) / np.float32(DST)
+        if y_ratio < 2 or row % 16 or (self.i420 and (self.src_w // 2) % 16):
+            return self.frame_bytes, False
+        ys = np.minimum((y_ratio * np.arange(DST, dtype=np.float32)).astype(np.int64), self.src_h - 2)
+        luma = np.unique(np.concatenate([ys, ys + 1]))
+        total = len(luma) * row
+        if self.i420:
+            total += 2 * len(np.unique(np.minimum(luma >> 1, self.src_h // 2 - 1))) * (self.src_w // 2)
+        return int(total), True
 
 
-def set_workload(name: str) -> None:
-    """Default = BASELINE.json configs[1]+[2] (the metric's configuration).  "4k-i420" = configs[3]: 4K planar
-    YUV420 camera frames (src/ffi/c_api/tk_ffi_api.c:917-931) through the full pre + post pipeline."""
-    global SRC_W, SRC_H, FRAME_BYTES, ALG_PRE, I420, METRIC, SRC_NAME
-    if name == "4k-i420":
-        SRC_W, SRC_H, I420, SRC_NAME = 3840, 2160, True, "4K I420"
-        FRAME_BYTES = SRC_W * SRC_H * 3 // 2
-        METRIC = "frames/s (pre+decode+NMS, 4K I420->640^2)"
-    ALG_PRE = FRAME_BYTES + TENSOR_BYTES_F16
+WORKLOADS = {
+    # BASELINE.json configs[1] + [2]: the configuration the metric is quoted on
+    "1080p-rgb": Workload("1080p-rgb", 1920, 1080, False, "1080p RGB8", 64),
+    # configs[3]: 4K planar YUV420 camera frames (src/ffi/c_api/tk_ffi_api.c:917-931), 32 per stream / GPU
+    "4k-i420": Workload("4k-i420", 3840, 2160, True, "4K I420", 32),
+}
 
 
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
-def make_inputs(batch: int, seed0: int):
-    """Seeded synthetic batch: `batch` random 1080p RGB8 frames + `batch` detector-head tensors."""
+def make_inputs(wl: Workload, batch: int, seed0: int):
+    """Seeded synthetic batch: `batch` random frames + `batch` detector-head tensors."""
     import synth
-    frames = np.empty((batch, FRAME_BYTES), np.uint8) if I420 else np.empty((batch, SRC_H, SRC_W, 3), np.uint8)
+    frames = np.empty((batch, wl.frame_bytes), np.uint8) if wl.i420 else np.empty((batch, wl.src_h, wl.src_w, 3), np.uint8)
     logits = np.empty((batch, P, 5 + NC), np.float32)
     for i in range(batch):
-        frames[i] = synth.i420_frame(SRC_W, SRC_H, seed0 + i) if I420 else synth.rgb_frame(SRC_W, SRC_H, seed0 + i)
+        frames[i] = synth.i420_frame(wl.src_w, wl.src_h, seed0 + i) if wl.i420 else synth.rgb_frame(wl.src_w, wl.src_h, seed0 + i)
         logits[i] = synth.logits_tensor(seed0 + i, adversarial=(i == 0))
     return frames, logits
+
+
+def post_touched_min_bytes(logits: np.ndarray) -> int:
+    """What decode must touch in DRAM per launch: one 32-byte sector per row for its objectness word plus the
+    surviving rows in full (340 B = up to 12 sectors) — the reference loop reads the rest of a row only behind
+    `row[4] > thr` (src/vision/tk_object_detector.c:345)."""
+    with np.errstate(invalid="ignore"):
+        surv = int(np.minimum((logits[:, :, 4] > CONF_THR).sum(axis=1), 4096).sum())
+    return logits.shape[0] * P * 32 + surv * 12 * 32
 
 
 # --------------------------------------------------------------------------- #
@@ -102,9 +135,10 @@ class CpuPath:
     reference has no fp16 output) + decode + class-wise NMS.  One frame per thread — the reference
     function is re-entrant."""
 
-    def __init__(self, threads: int):
+    def __init__(self, wl: Workload, threads: int):
         from oracle import oracle as O
         self.O = O
+        self.wl = wl
         self.threads = threads
         self.kind = "reference" if O.have_ref() else "port"
         self.lib = O.lib()
@@ -119,23 +153,23 @@ class CpuPath:
             t.out = np.empty((3, DST, DST), np.float32)
             t.cand = np.zeros(4096, self.O.CAND_DTYPE)
             t.kept = np.zeros(MAX_DET, self.O.CAND_DTYPE)
-            t.rgb = np.empty((SRC_H, SRC_W, 3), np.uint8) if I420 else None
+            t.rgb = np.empty((self.wl.src_h, self.wl.src_w, 3), np.uint8) if self.wl.i420 else None
         return t
 
     def one(self, frame: np.ndarray, logits: np.ndarray) -> int:
         t = self._bufs()
-        O = self.O
-        if I420:      # the reference has no YUV arithmetic: the oracle's BT.601 conversion, then its pre-processor
-            self.lib.oracle_i420_to_rgb8(frame.ctypes.data_as(C.c_void_p), C.c_uint32(SRC_W), C.c_uint32(SRC_H),
+        O, wl = self.O, self.wl
+        if wl.i420:   # the reference has no YUV arithmetic: the oracle's BT.601 conversion, then its pre-processor
+            self.lib.oracle_i420_to_rgb8(frame.ctypes.data_as(C.c_void_p), C.c_uint32(wl.src_w), C.c_uint32(wl.src_h),
                                          t.rgb.ctypes.data_as(C.c_void_p))
             frame = t.rgb
         if self.ref is not None:
-            vf = O._VideoFrame(SRC_W, SRC_H, SRC_W * 3, 0, frame.ctypes.data)
+            vf = O._VideoFrame(wl.src_w, wl.src_h, wl.src_w * 3, 0, frame.ctypes.data)
             rc = self.ref.tk_preprocessor_resize_and_normalize_to_chw(
                 C.byref(vf), t.out.ctypes.data_as(C.c_void_p), C.c_uint32(DST), C.c_uint32(DST), self.mean, self.std)
         else:
-            rc = self.lib.oracle_preprocess_rgb8(frame.ctypes.data_as(C.c_void_p), C.c_uint32(SRC_W), C.c_uint32(SRC_H),
-                                                 C.c_uint32(SRC_W * 3), t.out.ctypes.data_as(C.c_void_p), C.c_uint32(DST),
+            rc = self.lib.oracle_preprocess_rgb8(frame.ctypes.data_as(C.c_void_p), C.c_uint32(wl.src_w), C.c_uint32(wl.src_h),
+                                                 C.c_uint32(wl.src_w * 3), t.out.ctypes.data_as(C.c_void_p), C.c_uint32(DST),
                                                  C.c_uint32(DST), self.mean, self.std, C.c_int(0), C.c_int(0), C.c_float(0))
         assert rc == 0
         total = self.lib.oracle_decode(logits.ctypes.data_as(C.c_void_p), C.c_uint32(P), C.c_uint32(NC),
@@ -154,16 +188,16 @@ class CpuPath:
         pre = ("reference tk_preprocessor_resize_and_normalize_to_chw compiled from the reference tree (oracle/_ref, "
                "gcc -O2 -mavx, fp32 CHW out)" if self.kind == "reference"
                else "C restatement of the reference pre-processor (oracle/, fp32 CHW out)")
-        return (f"{frames_done} frames of the bench workload ({SRC_NAME} -> 640x640 + 25200x85 decode + class-wise NMS), "
+        return (f"{frames_done} frames of the bench workload ({self.wl.src_name} -> 640x640 + 25200x85 decode + class-wise NMS), "
                 f"{pre} + CPU restatement of decode/NMS (the reference's postprocess_detections is a stub), "
                 f"one frame per thread, {self.threads} threads")
 
 
-def cpu_baseline(frames: np.ndarray, logits: np.ndarray, target_cpu_seconds: float = 16.0) -> dict:
+def cpu_baseline(wl: Workload, frames: np.ndarray, logits: np.ndarray, target_cpu_seconds: float = 14.0) -> dict:
     """Bounded sample of the same workload on the host cores (rank 0, N=1 only)."""
     from concurrent.futures import ThreadPoolExecutor
     threads = os.cpu_count() or 1
-    cpu = CpuPath(threads)
+    cpu = CpuPath(wl, threads)
     with ThreadPoolExecutor(threads) as pool:
         sub = min(frames.shape[0], max(threads, 16))
         t_probe = cpu.run_batch(frames[:sub], logits[:sub], pool)            # warm-up + cost probe
@@ -175,6 +209,28 @@ def cpu_baseline(frames: np.ndarray, logits: np.ndarray, target_cpu_seconds: flo
             t += cpu.run_batch(frames, logits, pool)
     done = reps * frames.shape[0]
     return {"value": done / t, "unit": "frames/s", "cores": threads, "kind": cpu.kind, "sample": cpu.describe(done)}
+
+
+def cpu_sweep(wl: Workload, frames: np.ndarray, logits: np.ndarray, batches: list[int], seconds_each: float = 2.5) -> dict:
+    """The CPU arm at each sweep batch size: a batch of B frames is handed to the pool at once and waited for, as the
+    GPU call is (B < threads leaves cores idle — that is the point of the column).  Bounded: batches above the
+    generated 64 frames reuse them cyclically, and each point stops after `seconds_each`."""
+    from concurrent.futures import ThreadPoolExecutor
+    threads = os.cpu_count() or 1
+    cpu = CpuPath(wl, threads)
+    out = {}
+    base = frames.shape[0]
+    with ThreadPoolExecutor(threads) as pool:
+        for b in batches:
+            done, t = 0, 0.0
+            while t < seconds_each and done < 4 * max(b, threads):
+                idx = [(done + i) % base for i in range(min(b, 256))]      # at most 256 frames of a 1024 batch per pass
+                t0 = time.perf_counter()
+                list(pool.map(lambda i: cpu.one(frames[i], logits[i]), idx))
+                t += time.perf_counter() - t0
+                done += len(idx)
+            out[str(b)] = {"value": done / t, "frames_timed": done}
+    return {"unit": "frames/s", "cores": threads, "kind": cpu.kind, "by_batch": out}
 
 
 # --------------------------------------------------------------------------- #
@@ -235,12 +291,12 @@ class ClockSampler:
 # --------------------------------------------------------------------------- #
 # Reference arm                                                                 #
 # --------------------------------------------------------------------------- #
-def config_dict(n_gpus: int, batch: int) -> dict:
-    return {"workload": f"{SRC_NAME} x{batch} per GPU -> 640x640 fp16 NCHW (stretch-bilinear, ImageNet mean/std) + "
+def config_dict(wl: Workload, n_gpus: int, batch: int) -> dict:
+    return {"workload": f"{wl.src_name} x{batch} per GPU -> 640x640 fp16 NCHW (stretch-bilinear, ImageNet mean/std) + "
                         f"decode(raw, conf>{CONF_THR}) + class-wise NMS(IoU>{IOU_THR}, max {MAX_DET}) of {batch} tensors 25200x85 fp32",
-            "frames_per_gpu": batch, "global_batch": batch * n_gpus, "src": [SRC_W, SRC_H], "dst": [DST, DST],
+            "frames_per_gpu": batch, "global_batch": batch * n_gpus, "src": [wl.src_w, wl.src_h], "dst": [DST, DST],
             "proposals": P, "classes": NC, "sharding": f"frames x{n_gpus}, no collective",
-            "l2": "inputs larger than L2: %.0f MB of frames + logits read per step per GPU" % (batch * (FRAME_BYTES + LOGIT_BYTES) / 1e6)}
+            "l2": "inputs larger than L2: %.0f MB of frames + logits read per step per GPU" % (batch * (wl.frame_bytes + LOGIT_BYTES) / 1e6)}
 
 
 def run_reference(args) -> None:
@@ -248,9 +304,10 @@ def run_reference(args) -> None:
     if rank != 0:
         return                                   # rank 0 alone runs the CPU arm
     from concurrent.futures import ThreadPoolExecutor
-    frames, logits = make_inputs(args.batch, 0)
+    wl = WORKLOADS[args.workload]
+    frames, logits = make_inputs(wl, args.batch, 0)
     threads = os.cpu_count() or 1
-    cpu = CpuPath(threads)
+    cpu = CpuPath(wl, threads)
     with ThreadPoolExecutor(threads) as pool:
         for _ in range(args.warmup):
             cpu.run_batch(frames, logits, pool)
@@ -258,10 +315,10 @@ def run_reference(args) -> None:
         for _ in range(args.steps):
             t += cpu.run_batch(frames, logits, pool)
     fps = args.steps * args.batch / t
-    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": wl.metric, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args.gpus, args.batch),
+            "config": config_dict(wl, args.gpus, args.batch),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": cpu.kind,
                              "sample": cpu.describe(args.steps * args.batch) + f"; each step = one {args.batch}-frame batch"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -273,8 +330,8 @@ def run_reference(args) -> None:
 # B200 arm                                                                      #
 # --------------------------------------------------------------------------- #
 def load_traffic() -> dict:
-    """ncu dram bytes per launch of each kernel at this workload, written from a --set full capture
-    (profiles/traffic.json); absent -> null."""
+    """ncu dram bytes per launch of each kernel at the default workload, written from a --set full capture
+    (profiles/traffic.json: {"commit": ..., "kernels": {...}}); absent -> {}."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             return json.load(f)
@@ -282,184 +339,418 @@ def load_traffic() -> dict:
         return {}
 
 
-def run_b200(args) -> None:
-    import torch
-    import torch.distributed as dist
-    from trackiellm_b200 import _capi as capi
-    from trackiellm_b200 import vision as V
+def git_head() -> str | None:
+    try:
+        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True,
+                              timeout=5).stdout.strip() or None
+    except Exception:
+        return None
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; libtk_b200 has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        # frames shard with no data-path collective; gloo only carries the barrier and the max
-        dist.init_process_group("gloo", rank=rank, world_size=world)
-    dev = torch.device("cuda", local)
-    B, K, W = args.batch, args.steps, args.warmup
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+class Ctx:
+    """Per-process state shared by the measurements."""
 
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; libtk_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            # frames shard with no data-path collective; gloo only carries the barrier and the max
+            dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
+        self.dev = torch.device("cuda", self.local)
+        self.args = args
+        from trackiellm_b200 import _capi as capi
+        self.lib = capi.lib()
+        self.lib.tk_b200_launch_count.restype = C.c_ulonglong
+        self.sampler = ClockSampler(self.local)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+
+    def max_over_ranks(self, x: float) -> float:
+        if self.world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([x], dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t[0])
 
-    frames_np, logits_np = make_inputs(B, rank * B)
-    h_frames = torch.from_numpy(frames_np).pin_memory()
-    h_logits = torch.from_numpy(logits_np).pin_memory()
-    d_frames = h_frames.to(dev)
-    d_logits = h_logits.to(dev)
+    def launches(self) -> int:
+        return int(self.lib.tk_b200_launch_count())
 
-    pipe = V.Pipeline(device_id=local, max_batch=B, chunk_frames=args.chunk, width=SRC_W, height=SRC_H,
-                      fmt=V.PIXEL_I420 if I420 else V.PIXEL_RGB8,
-                      tensor_w=DST, tensor_h=DST, out_dtype=torch.float16, num_proposals=P, num_classes=NC,
-                      act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR, max_detections=MAX_DET,
-                      stage_host_logits=args.logits_mode)
-    d_tensor, d_dets, d_counts = pipe.alloc_outputs(B)
-    _, h_dets, h_counts = pipe.alloc_outputs(B, pinned=True)
-    lib = capi.lib()
-    lib.tk_b200_launch_count.restype = C.c_ulonglong
-    sampler = ClockSampler(local)
 
-    # ---------------- device-resident: `value` ----------------
-    for _ in range(max(W, 3)):
+def make_pipe(ctx: Ctx, wl: Workload, max_batch: int, arith: str):
+    from trackiellm_b200 import vision as V
+    return V.Pipeline(device_id=ctx.local, max_batch=max_batch, chunk_frames=ctx.args.chunk, width=wl.src_w, height=wl.src_h,
+                      fmt=V.PIXEL_I420 if wl.i420 else V.PIXEL_RGB8, tensor_w=DST, tensor_h=DST, out_dtype=ctx.torch.float16,
+                      num_proposals=P, num_classes=NC, act=V.ACT_RAW, conf_thr=CONF_THR, iou_thr=IOU_THR,
+                      max_detections=MAX_DET, stage_host_logits=ctx.args.logits_mode,
+                      arith={"exact": V.ARITH_EXACT, "half": V.ARITH_HALF, "fast": V.ARITH_FAST}[arith],
+                      fuse_postprocess=ctx.args.fuse)
+
+
+def timed_device(ctx: Ctx, pipe, d_frames, d_logits, outs, K: int, W: int):
+    """W warm-up steps, then K steps of tk_b200_pipeline_process_device bracketed by CUDA events on the launching stream,
+    barrier + synchronize on both sides; returns (ms for K steps, max over ranks; kernels launched)."""
+    torch = ctx.torch
+    d_tensor, d_dets, d_counts = outs
+    for _ in range(W):
         pipe.process_device(d_frames, d_logits, d_tensor, d_dets, d_counts)
-    barrier()
-    # The timed region is the call a user makes: K steps with nothing between the kernels.  The per-kernel
-    # durations come from a second K-step pass right behind it, same inputs, with CUDA events recorded on the
-    # launching stream between the kernels; the four records serialise kernel tail and next launch and cost
-    # about 12 us of a 151 us step on B200 (tools/exp_pdl.py), which is why they are not inside `value`.
+    ctx.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = int(lib.tk_b200_launch_count())
-    sampler.resume()
+    l0 = ctx.launches()
     e0.record()
     for _ in range(K):
         pipe.process_device(d_frames, d_logits, d_tensor, d_dets, d_counts)
     e1.record()
-    barrier()
-    launches = int(lib.tk_b200_launch_count()) - launches0
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ctx.barrier()
+    return ctx.max_over_ranks(e0.elapsed_time(e1)), ctx.launches() - l0
+
+
+def timed_host(ctx: Ctx, pipe, h_frames, logits, h_dets, h_counts, steps: int, tensor=None, logits_on_device=False) -> float:
+    """2 warm-up calls, then `steps` blocking process_host calls; wall clock, max over ranks (seconds)."""
+    for _ in range(2):
+        pipe.process_host(h_frames, logits, h_dets, h_counts, tensor=tensor, logits_on_device=logits_on_device)
+    ctx.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pipe.process_host(h_frames, logits, h_dets, h_counts, tensor=tensor, logits_on_device=logits_on_device)
+    ctx.torch.cuda.synchronize()
+    s = ctx.max_over_ranks(time.perf_counter() - t0)
+    ctx.barrier()
+    return s
+
+
+def stage_report(ctx: Ctx, wl: Workload, pipe, d_frames, d_logits, outs, K: int, B: int, logits_np, peak: float,
+                 traffic: dict) -> tuple[list, float]:
+    """Per-kernel durations from CUDA events recorded by the library between the launches, in a K-step pass of its own
+    (the records cost a few us per step, so they are not inside `value`)."""
+    torch = ctx.torch
+    d_tensor, d_dets, d_counts = outs
     pipe.stage_timing(K)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     for _ in range(K):
         pipe.process_device(d_frames, d_logits, d_tensor, d_dets, d_counts)
     e3.record()
-    barrier()
-    sampler.pause()
-    ms_total_staged = max_over_ranks(e2.elapsed_time(e3))
+    ctx.barrier()
+    ms_staged = ctx.max_over_ranks(e2.elapsed_time(e3))
     stage_ms, calls = pipe.stage_times()
     pipe.stage_timing(0)
-    dev_counts = d_counts.cpu().numpy().copy()
-    dev_cand_counts = (logits_np[:, :, 4] > CONF_THR).sum(axis=1)      # rows that pass the threshold (read in full by decode)
-    dev_dets = d_dets.cpu().numpy().copy()
+    per = [m / max(calls, 1) for m in stage_ms]
+    fused = per[2] == 0.0 and per[1] > 0.0
+    post_min = post_touched_min_bytes(logits_np)
+    kern = traffic.get("kernels", {})
+    stages = []
+
+    def entry(name, ms, alg, note=None, min_touched=None):
+        e = {"kernel": name, "ms_per_launch": ms, "algorithmic_bytes_per_launch": alg}
+        ach = alg / (ms * 1e-3) / 1e9 if ms > 0 and alg else None
+        e["achieved"], e["frac"] = ach, (ach / peak if ach else None)
+        t = kern.get(name)
+        e["traffic"] = t
+        if t and ms > 0:
+            e["frac_touched"] = t / (ms * 1e-3) / 1e9 / peak          # ncu dram bytes / time / peak
+        if min_touched is not None:
+            e["min_touched_bytes_per_launch"] = min_touched
+        if note:
+            e["note"] = note
+        return e
+
+    stages.append(entry("preprocess_kernel", per[0], wl.alg_pre * B))
+    whole = ("SURVEY §8(d) counts every logit byte once (%d B per launch); the kernel, like the reference loop "
+             "(tk_object_detector.c:345), reads only the objectness word of a rejected row, so algorithmic_bytes_per_launch "
+             "here is what must be touched (one 32-B sector per row + the surviving rows) and frac_touched is the ncu DRAM "
+             "bytes / time / peak" % (LOGIT_BYTES * B))
+    if fused:
+        stages.append(entry("post_kernel", per[1], post_min, min_touched=post_min,
+                            note="decode + class-wise NMS fused per frame, one persistent 256-thread CTA per SM on a second "
+                                 "stream, RESIDENT BESIDE the pre-process kernel: its duration (from the fork) overlaps "
+                                 "ms_per_launch of preprocess_kernel and is latency-bound by design. " + whole))
+    else:
+        stages.append(entry("decode_kernel", per[1], post_min, min_touched=post_min, note=whole))
+        stages.append(entry("nms_kernel", per[2], 0, note="shared memory only; latency-bound"))
+    return stages, ms_staged
+
+
+def h2d_rate(ctx: Ctx, h_buf, d_buf, reps: int = 6) -> float:
+    """Raw pinned host->device copy rate of this rank's link, every rank copying at once (GB/s per rank, from the
+    slowest rank's time)."""
+    torch = ctx.torch
+    d_buf.copy_(h_buf, non_blocking=True)
+    ctx.barrier()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        d_buf.copy_(h_buf, non_blocking=True)
+    torch.cuda.synchronize()
+    s = ctx.max_over_ranks(time.perf_counter() - t0)
+    ctx.barrier()
+    return reps * h_buf.numel() * h_buf.element_size() / s / 1e9
+
+
+def measure_workload(ctx: Ctx, wl: Workload, B: int, K: int, W: int, *, full: bool) -> dict:
+    """Device-resident value (+ roofline stages), e2e through the host-buffer call; `full` adds the HALF arithmetic
+    figures, e2e_with_tensor, e2e_device_logits and the link ceiling (the headline workload)."""
+    torch = ctx.torch
+    args = ctx.args
+    frames_np, logits_np = make_inputs(wl, B, ctx.rank * B)
+    h_frames = torch.from_numpy(frames_np).pin_memory()
+    h_logits = torch.from_numpy(logits_np).pin_memory()
+    d_frames, d_logits = h_frames.to(ctx.dev), h_logits.to(ctx.dev)
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    traffic = load_traffic() if wl.key == "1080p-rgb" and B == 64 else {}     # the ncu capture is of the default workload
+    res: dict = {}
+
+    pipe = make_pipe(ctx, wl, B, args.arith)
+    outs = pipe.alloc_outputs(B)
+    _, h_dets, h_counts = pipe.alloc_outputs(B, pinned=True)
+
+    # ---------------- device-resident: `value` ----------------
+    ctx.sampler.resume()
+    ms_total, launches = timed_device(ctx, pipe, d_frames, d_logits, outs, K, max(W, 3))
+    stages, ms_staged = stage_report(ctx, wl, pipe, d_frames, d_logits, outs, K, B, logits_np, peak, traffic)
+    ctx.sampler.pause()
+    dev_counts = outs[2].cpu().numpy().copy()
+    dev_dets = outs[1].cpu().numpy().copy()
+    with np.errstate(invalid="ignore"):
+        dev_cand_counts = (logits_np[:, :, 4] > CONF_THR).sum(axis=1)  # rows that pass the threshold (read in full by decode)
+    step_ms = ms_total / K
+    d = stages[0]                                                      # the pre-process kernel: the step's dominant kernel
+    for s in stages:
+        if s["kernel"] != "post_kernel" and s["ms_per_launch"] > d["ms_per_launch"]:
+            d = s
+    post_min = post_touched_min_bytes(logits_np)
+    res.update({
+        "value": ctx.world * B * K / (ms_total * 1e-3), "ms_per_step": step_ms, "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "kernel": d["kernel"], "achieved": d["achieved"], "peak": peak, "unit": "GB/s",
+                     "frac": d["frac"], "traffic": d["traffic"], "traffic_captured_at": traffic.get("commit"),
+                     "peak_source": peak_src, "ms_per_launch": d["ms_per_launch"],
+                     "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
+                     "share_of_step": d["ms_per_launch"] / max(step_ms, 1e-12),
+                     "arith": args.arith,
+                     "timed_by": "CUDA events recorded by the library on the launching stream(s) around the kernels, in a K-step "
+                                 "pass of its own right after the timed region (same inputs); ms_per_step_with_stage_events is "
+                                 "that pass's step time",
+                     "ms_per_step_with_stage_events": ms_staged / K},
+        "roofline_stages": stages,
+        "roofline_step": {"bytes_per_step": wl.alg_pre * B + post_min,
+                          "definition": "pre-process: every source byte + every tensor byte once; post-process: one 32-B sector "
+                                        "per logit row + the surviving rows (what decode must touch)",
+                          "achieved": (wl.alg_pre * B + post_min) / (step_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                          "frac": (wl.alg_pre * B + post_min) / (step_ms * 1e-3) / 1e9 / peak},
+        "detections_per_frame": float(np.mean(dev_counts)),
+    })
 
     # ---------------- end to end through the host-buffer C-ABI call: `e2e` ----------------
     Ke = max(2, min(K, args.e2e_steps))
-    for _ in range(2):
-        pipe.process_host(h_frames, h_logits, h_dets, h_counts)
-    barrier()
-    sampler.resume()
-    t0 = time.perf_counter()
-    for _ in range(Ke):
-        pipe.process_host(h_frames, h_logits, h_dets, h_counts)
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    sampler.pause()
-    barrier()
-    # same, with the logits left on the device by a co-located detector (informative)
-    t0 = time.perf_counter()
-    for _ in range(Ke):
-        pipe.process_host(h_frames, d_logits, h_dets, h_counts, logits_on_device=True)
-    torch.cuda.synchronize()
-    e2e_dl_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
-    # the host path must give what the device path gave
+    frame_pcie, frames_in_place = wl.frame_bytes_over_pcie()
+    ctx.sampler.resume()
+    e2e_s = timed_host(ctx, pipe, h_frames, h_logits, h_dets, h_counts, Ke)
+    ctx.sampler.pause()
     hc = h_counts.numpy()
     same = bool(np.array_equal(hc, dev_counts)) and all(
         np.array_equal(h_dets.numpy()[i, :hc[i]], dev_dets[i, :hc[i]]) for i in range(B))
     if not same:
         raise SystemExit("bench.py: host-buffer path and device-resident path disagree")
-    clocks = sampler.result()
-
-    if rank == 0:
-        peaks = {}
-        try:
-            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-                peaks = json.load(f)
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        names = ["preprocess_kernel", "decode_kernel", "nms_kernel"]
-        alg = [ALG_PRE * B, ALG_POST * B, 0]
-        per_launch_ms = [m / max(calls, 1) for m in stage_ms]
-        traffic = {} if I420 else load_traffic()          # the ncu capture is of the default workload
-        stages = []
-        for nme, a, m in zip(names, alg, per_launch_ms):
-            ach = a / (m * 1e-3) / 1e9 if m > 0 and a else None
-            stages.append({"kernel": nme, "ms_per_launch": m, "algorithmic_bytes_per_launch": a,
-                           "achieved": ach, "frac": (ach / peak) if ach else None, "traffic": traffic.get(nme)})
-        dom = max(range(3), key=lambda i: per_launch_ms[i])
-        d = stages[dom]
-        roofline = {"bound": "hbm", "kernel": d["kernel"], "achieved": d["achieved"], "peak": peak, "unit": "GB/s",
-                    "frac": d["frac"], "traffic": d["traffic"], "peak_source": peak_src,
-                    "ms_per_launch": d["ms_per_launch"], "algorithmic_bytes_per_launch": d["algorithmic_bytes_per_launch"],
-                    "share_of_step": d["ms_per_launch"] / max(sum(per_launch_ms), 1e-12),
-                    "timed_by": "CUDA events on the launching stream between the kernels, in a second K-step pass right after "
-                                "the timed region (same inputs); ms_per_step_with_stage_events is that pass's step time",
-                    "ms_per_step_with_stage_events": ms_total_staged / K}
-        frame_pcie, frames_in_place = frame_bytes_over_pcie()
-        step_ms = ms_total / K
-        step_ach = (ALG_PRE + ALG_POST) * B / (step_ms * 1e-3) / 1e9
-        line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": "frames/s", "n_gpus": world,
-                "steps": K, "warmup": max(W, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": ("i32 BT.601 + f32 lerp -> f16 tensor (pre-process); f32 / i32 (decode, NMS, bit-exact)" if I420 else
-                          "f16 lerp -> f16 tensor (pre-process, within the 1e-2 fp16 bar); f32 / i32 (decode, NMS, bit-exact)"),
-                "data": "synthetic", "config": config_dict(world, B),
-                "roofline": roofline, "roofline_stages": stages,
-                "roofline_step": {"algorithmic_bytes_per_frame": ALG_PRE + ALG_POST, "achieved": step_ach, "peak": peak,
-                                  "unit": "GB/s", "frac": step_ach / peak},
-                "e2e": {"value": world * B * Ke / e2e_s, "unit": "frames/s",
-                        "h2d_bytes_per_step": B * ((0 if frames_in_place else FRAME_BYTES)
-                                                   + (LOGIT_BYTES, P * 4, 0)[(1, 0, 2).index(args.logits_mode)]),
-                        "host_bytes_read_in_place_per_step": (B * frame_pcie if frames_in_place else 0) + (
-                            0 if args.logits_mode == 1 else int(np.sum(np.minimum(dev_cand_counts, 4096))) * (5 + NC) * 4
-                            + (B * P * 64 if args.logits_mode == 2 else 0)),
-                        "d2h_bytes_per_step": B * (MAX_DET * 28 + 4), "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke,
-                        "api": "tk_b200_pipeline_process_host (pinned host frames + logits in, host detections + counts out; "
-                               "the fp16 tensors stay on the device for the detector); "
-                               + ("the pinned frames are read in place by the pre-process kernel's row ring (only the two source "
-                                  "rows of each output row cross PCIe: %d of %d bytes per frame), " % (frame_pcie, FRAME_BYTES)
-                                  if frames_in_place else "frames are copied H2D in chunks, ")
-                               + {1: "logits are copied H2D in chunks",
-                                  2: "the pinned logits are read in place over PCIe by decode_kernel (objectness word of every "
-                                     "row, 64 B per request, + surviving rows), not copied",
-                                  0: "the pinned logits stay in host memory: their objectness column (4 of every 340 bytes) is "
-                                     "packed by 4 host threads while the frame copies run and uploaded as one dense array; "
-                                     "decode_kernel reads only the surviving rows in place over PCIe"}[args.logits_mode]},
-                "e2e_device_logits": {"value": world * B * Ke / e2e_dl_s, "unit": "frames/s",
-                                      "h2d_bytes_per_step": 0 if frames_in_place else B * FRAME_BYTES,
-                                      "host_bytes_read_in_place_per_step": B * frame_pcie if frames_in_place else 0,
-                                      "d2h_bytes_per_step": B * (MAX_DET * 28 + 4),
-                                      "api": "tk_b200_pipeline_process_host_frames (logits already in HBM)"},
-                "gpu_launches": launches, "clocks": clocks,
-                "detections_per_frame": float(np.mean(dev_counts))}
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(frames_np, logits_np)
-        print(json.dumps(line), flush=True)
+    logit_h2d = (LOGIT_BYTES, P * 4, 0)[(1, 0, 2).index(args.logits_mode)]
+    rows_in_place = 0 if args.logits_mode == 1 else (int(np.sum(np.minimum(dev_cand_counts, 4096))) * (5 + NC) * 4
+                                                     + (B * P * 64 if args.logits_mode == 2 else 0))
+    in_place = (B * frame_pcie if frames_in_place else 0) + rows_in_place
+    api = ("tk_b200_pipeline_process_host (pinned host frames + logits in, host detections + counts out; "
+           "the fp16 tensors stay on the device for the detector — see e2e_with_tensor for the call that also returns them); "
+           + ("the pinned frames are read in place by the pre-process kernel's row ring (only the two source "
+              "rows of each output row cross PCIe: %d of %d bytes per frame), " % (frame_pcie, wl.frame_bytes)
+              if frames_in_place else "frames are copied H2D in chunks, ")
+           + {1: "logits are copied H2D in chunks",
+              2: "the pinned logits are read in place over PCIe by the decode pass (objectness word of every "
+                 "row, 64 B per request, + surviving rows), not copied",
+              0: "the pinned logits stay in host memory: their objectness column (4 of every 340 bytes) is "
+                 "packed by the handle's host threads while the frame copies run and uploaded as one dense array; "
+                 "the decode pass reads only the surviving rows in place over PCIe"}[args.logits_mode])
+    h2d = B * ((0 if frames_in_place else wl.frame_bytes) + logit_h2d)
+    res["e2e"] = {"value": ctx.world * B * Ke / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
+                  "host_bytes_read_in_place_per_step": in_place, "d2h_bytes_per_step": B * DET_BYTES, "steps": Ke,
+                  "ms_per_step": 1e3 * e2e_s / Ke, "api": api}
+    if full:
+        # the tensors come back too (what the CPU arm leaves in host memory, here in fp16)
+        h_tensor = torch.empty((B, 3, DST, DST), dtype=torch.float16).pin_memory()
+        s = timed_host(ctx, pipe, h_frames, h_logits, h_dets, h_counts, Ke, tensor=h_tensor)
+        if not torch.equal(h_tensor, outs[0].cpu()):
+            raise SystemExit("bench.py: tensors returned by the host-buffer path differ from the device-resident ones")
+        res["e2e_with_tensor"] = {"value": ctx.world * B * Ke / s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
+                                  "host_bytes_read_in_place_per_step": in_place,
+                                  "d2h_bytes_per_step": B * (DET_BYTES + TENSOR_BYTES_F16), "ms_per_step": 1e3 * s / Ke,
+                                  "api": "tk_b200_pipeline_process_host with h_tensor: as e2e, and the fp16 NCHW tensors are "
+                                         "copied back to pinned host memory inside the call"}
+        del h_tensor
+        # logits left on the device by a co-located detector (informative)
+        s = timed_host(ctx, pipe, h_frames, d_logits, h_dets, h_counts, Ke, logits_on_device=True)
+        res["e2e_device_logits"] = {"value": ctx.world * B * Ke / s, "unit": "frames/s",
+                                    "h2d_bytes_per_step": 0 if frames_in_place else B * wl.frame_bytes,
+                                    "host_bytes_read_in_place_per_step": B * frame_pcie if frames_in_place else 0,
+                                    "d2h_bytes_per_step": B * DET_BYTES,
+                                    "api": "tk_b200_pipeline_process_host_frames (logits already in HBM)"}
+        # raw link: what a perfect overlap of everything else would leave
+        gbs = h2d_rate(ctx, h_frames, d_frames)
+        per_frame = (frame_pcie if frames_in_place else wl.frame_bytes) + logit_h2d + rows_in_place / B
+        res["e2e_link_ceiling"] = {"value": ctx.world * gbs * 1e9 / per_frame, "unit": "frames/s",
+                                   "h2d_gbs_per_gpu_all_ranks_copying": gbs, "bytes_over_the_link_per_frame": per_frame,
+                                   "e2e_over_ceiling": res["e2e"]["value"] / (ctx.world * gbs * 1e9 / per_frame),
+                                   "how": "pinned cudaMemcpyAsync of this rank's frame batch, every rank copying at once, wall "
+                                          "clock, max over ranks; frames/s = ranks x GB/s / bytes a frame moves over PCIe in e2e"}
     pipe.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+
+    if full and args.arith != "half" and not wl.i420:
+        # ---------------- the same workload in HALF arithmetic (labelled extra; within the fp16 bar, not bit-exact) --------
+        pipe = make_pipe(ctx, wl, B, "half")
+        ms_h, _ = timed_device(ctx, pipe, d_frames, d_logits, outs, K, max(W, 3))
+        st_h, _ = stage_report(ctx, wl, pipe, d_frames, d_logits, outs, K, B, logits_np, peak, {})
+        pipe.close()
+        res["half"] = {"value": ctx.world * B * K / (ms_h * 1e-3), "unit": "frames/s", "ms_per_step": ms_h / K,
+                       "dtype": "f16 lerp (half2 HFMA2) -> f16 tensor: within 1e-2 + 1e-2|ref| of the reference (bound in DESIGN §3, "
+                                "tests/test_gpu_preprocess.py::test_half_arithmetic_adversarial_bound), not bit-exact",
+                       "roofline": {k: st_h[0][k] for k in ("kernel", "ms_per_launch", "algorithmic_bytes_per_launch", "achieved", "frac")}}
+    res["_inputs"] = (frames_np, logits_np)
+    return res
+
+
+def sweep(ctx: Ctx, wl: Workload, base_frames, base_logits, batches: list[int]) -> list:
+    """BASELINE configs[4]: global batch B sharded in contiguous blocks over the ranks (rank g owns
+    [g*B/G, (g+1)*B/G)), device-resident and end to end.  Frames beyond the generated 64 repeat them."""
+    torch = ctx.torch
+    from trackiellm_b200.shard import shard_range
+    base = base_frames.shape[0]
+    d_base_f, d_base_l = torch.from_numpy(base_frames).to(ctx.dev), torch.from_numpy(base_logits).to(ctx.dev)
+    rows = []
+    for Bg in batches:
+        lo, hi = shard_range(Bg, ctx.rank, ctx.world)
+        n = hi - lo
+        per_rank = max(Bg // ctx.world, 1)
+        K = int(max(5, min(100, 6400 // per_rank)))
+        Ke = int(max(3, min(20, 640 // per_rank)))
+        do_e2e = per_rank <= 256
+        row = {"global_batch": Bg, "steps": K}
+        e2e_s = None
+        if n > 0:
+            idx = torch.arange(lo, hi, device=ctx.dev) % base
+            d_f, d_l = d_base_f[idx].contiguous(), d_base_l[idx].contiguous()
+            pipe = make_pipe(ctx, wl, n, ctx.args.arith)
+            outs = pipe.alloc_outputs(n)
+            ms, _ = timed_device(ctx, pipe, d_f, d_l, outs, K, 3)
+            if do_e2e:
+                h_f, h_l = d_f.cpu().pin_memory(), d_l.cpu().pin_memory()
+                _, h_d, h_c = pipe.alloc_outputs(n, pinned=True)
+                e2e_s = timed_host(ctx, pipe, h_f, h_l, h_d, h_c, Ke)
+                del h_f, h_l
+            pipe.close()
+            del d_f, d_l, outs
+        else:                                    # a rank without frames still meets the barriers and the max
+            ctx.barrier(); ctx.barrier()
+            ms = ctx.max_over_ranks(0.0)
+            if do_e2e:
+                ctx.barrier()
+                e2e_s = ctx.max_over_ranks(0.0)
+                ctx.barrier()
+        row["value"] = Bg * K / (ms * 1e-3)
+        row["us_per_step"] = 1e3 * ms / K
+        if e2e_s is not None:
+            row["e2e"] = Bg * Ke / e2e_s
+            row["e2e_ms_per_step"] = 1e3 * e2e_s / Ke
+        rows.append(row)
+    return rows
+
+
+def detect_latency(ctx: Ctx) -> dict:
+    """BASELINE configs[0] through the reference's own call: tk_object_detector_detect on one HOST 640x480 RGB frame
+    (upload + pre-process fp32 + bound network + decode + NMS + malloc'd results), wall clock per blocking call.  The
+    network is a stand-in: a device-to-device copy of a prepared 25200x85 head tensor enqueued from the hook."""
+    import synth
+    from trackiellm_b200 import vision as V
+    torch = ctx.torch
+    cu = C.CDLL("libcuda.so.1")
+    frame = synth.rgb_frame(640, 480, 0)
+    lg = torch.from_numpy(synth.logits_tensor(0, adversarial=True)).to(ctx.dev)
+
+    def net(d_in, n, iw, ih, d_out, p, l, stream):
+        return cu.cuMemcpyDtoDAsync_v2(C.c_uint64(d_out), C.c_uint64(lg.data_ptr()), C.c_size_t(n * p * l * 4), C.c_void_p(stream))
+
+    with V.ObjectDetector(device_id=ctx.local, class_labels=[f"c{i}" for i in range(NC)], conf_thr=CONF_THR, iou_thr=IOU_THR) as det:
+        det.bind_network(net, P)
+        for _ in range(10):
+            r = det.detect(frame)
+        ts = []
+        for _ in range(200):
+            t0 = time.perf_counter()
+            r = det.detect(frame)
+            ts.append((time.perf_counter() - t0) * 1e6)
+    ts.sort()
+    return {"median": ts[100], "p90": ts[180], "calls": 200, "detections": len(r),
+            "what": "tk_object_detector_detect, one 640x480 RGB8 frame in pageable host memory -> 640x640 fp32 tensor -> "
+                    "stand-in network (D2D copy of a 25200x85 head tensor) -> decode + class-wise NMS -> malloc'd "
+                    "tk_detection_result_t[]; wall clock per blocking call"}
+
+
+def run_b200(args) -> None:
+    ctx = Ctx(args)
+    wl = WORKLOADS[args.workload]
+    B, K, W = args.batch, args.steps, args.warmup
+
+    head = measure_workload(ctx, wl, B, K, W, full=True)
+    frames_np, logits_np = head.pop("_inputs")
+    extras: dict = {}
+    if not args.only_headline:
+        other = WORKLOADS["4k-i420" if wl.key == "1080p-rgb" else "1080p-rgb"]
+        o = measure_workload(ctx, other, other.default_batch, max(10, K // 2), W, full=False)
+        o.pop("_inputs")
+        o["config"] = config_dict(other, ctx.world, other.default_batch)
+        o["metric"] = other.metric
+        if other.i420:
+            o["roofline"]["touched_note"] = ("4K -> 640: the mapping never samples 40.7 % of the luma rows and the kernel does not "
+                                              "fetch them, so frac is on the whole-frame algorithmic count (SURVEY §8d honesty rule)")
+        extras["workloads"] = {other.key: o}
+        if wl.key == "1080p-rgb":
+            extras["sweep"] = {"unit": "frames/s", "sharding": "global batch in contiguous blocks over the ranks",
+                               "points": sweep(ctx, wl, frames_np, logits_np, [1, 8, 64, 256, 1024])}
+        if ctx.rank == 0:
+            extras["detect_latency_us"] = detect_latency(ctx)
+        ctx.barrier()
+    clocks = ctx.sampler.result()
+
+    if ctx.rank == 0:
+        line = {"metric": wl.metric, "value": head.pop("value"), "unit": "frames/s", "n_gpus": ctx.world,
+                "steps": K, "warmup": max(W, 3), "ms_per_step": head.pop("ms_per_step"), "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None,
+                "dtype": {"exact": "f32 in the reference's operation order -> RNE f16 tensor (bit-exact to RNE of the reference's fp32 result)",
+                          "half": "f16 lerp -> f16 tensor (within the 1e-2 fp16 bar)",
+                          "fast": "f32 FMA lerp -> f16 tensor (within 1e-5 of the reference before rounding)"}[args.arith]
+                         + ("; i32 BT.601 16.16 YUV->RGB" if wl.i420 else "") + "; f32 / i32 decode + NMS (bit-exact)",
+                "data": "synthetic", "config": config_dict(wl, ctx.world, B)}
+        line.update(head)
+        line.update(extras)
+        line["clocks"] = clocks
+        line["commit"] = git_head()
+        if ctx.world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl, frames_np, logits_np)
+            if "sweep" in line:
+                line["sweep"]["cpu_arm"] = cpu_sweep(wl, frames_np, logits_np, [1, 8, 64, 256, 1024])
+        print(json.dumps(line), flush=True)
+    if ctx.world > 1:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
 
 
 def main() -> None:
@@ -468,19 +759,24 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="1080p-rgb", choices=["1080p-rgb", "4k-i420"],
-                    help="1080p-rgb: BASELINE configs[1]+[2], the metric's configuration (default); 4k-i420: configs[3]")
+    ap.add_argument("--workload", default="1080p-rgb", choices=list(WORKLOADS),
+                    help="the headline workload; 1080p-rgb: BASELINE configs[1]+[2], the metric's configuration (default); "
+                         "4k-i420: configs[3].  The other one is reported under `workloads`.")
     ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default 64; 32 for 4k-i420)")
     ap.add_argument("--chunk", type=int, default=8, help="frames per in-flight chunk of the host-buffer call")
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--only-headline", action="store_true", help="skip workloads / sweep / detect latency (experiments)")
+    ap.add_argument("--arith", default="exact", choices=["exact", "half", "fast"],
+                    help="pre-process arithmetic of the headline (default: the reference's, bit-exact)")
+    ap.add_argument("--fuse", type=int, default=0, choices=[0, 1, 2],
+                    help="decode + NMS as one co-resident kernel beside the pre-process kernel: 0 library default, 1 off, 2 on")
     ap.add_argument("--logits-mode", type=int, default=0, choices=[0, 1, 2],
                     help="e2e, host logits: 0 objectness column packed on the host + surviving rows in place (default), "
                          "1 whole tensor copied to HBM, 2 objectness and rows read in place over PCIe")
     args = ap.parse_args()
-    set_workload(args.workload)
     if args.batch <= 0:
-        args.batch = 32 if I420 else 64
+        args.batch = WORKLOADS[args.workload].default_batch
     if args.impl == "reference":
         run_reference(args)
     else:

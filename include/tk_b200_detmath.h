@@ -71,7 +71,7 @@ TK_DM_FN float tk_dm_div(float a, float b) {
 #endif
 }
 
-/* exp(x) in fp32, |rel err| < ~2 ulp, bit-identical on host and device.
+/* exp(x) in fp32, |err| < 3 ulp (measured 2.62), bit-identical on host and device.
  * n = round(x*log2e); r = x - n*ln2 (two-step Cody-Waite with fma);
  * e^r by a degree-6 Horner polynomial in fma; result scaled by 2^n through two
  * exact power-of-two multiplies so that gradual underflow is handled by the

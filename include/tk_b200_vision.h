@@ -178,6 +178,33 @@ typedef struct {
 
 TK_NODISCARD tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* params, cudaStream_t stream);
 
+/* Decode + class-wise NMS of whole frames in ONE kernel (decode_kernel + nms_kernel fused per frame; completes
+ * src/vision/tk_object_detector.c:343-357 in one pass).  Cut to 256 threads, <= 32 registers and 25 KB of shared
+ * memory per CTA so that it can be RESIDENT BESIDE another kernel (the pipeline runs it on a second stream under
+ * the pre-process kernel).  Same results, bit for bit, as tk_kernels_decode_detections followed by
+ * tk_kernels_nms_classwise; d_candidates / d_counts receive the intermediate list exactly as decode leaves it.
+ * Frames with more than 512 candidates run their NMS through d_workspace (global memory): slower, same result. */
+typedef struct {
+    const float*         d_logits;            /* [N][P][5+C] fp32 row-major                               */
+    uint32_t             num_frames, num_proposals, num_classes;
+    float                confidence_threshold;
+    tk_b200_activation_e activation;
+    tk_b200_candidate_t* d_candidates;        /* [N][max_candidates]                                      */
+    uint32_t*            d_counts;            /* [N] rows passing the threshold (may exceed the cap)      */
+    uint32_t             max_candidates;      /* <= 4096                                                  */
+    float                iou_threshold;
+    uint32_t             max_detections;
+    int                  class_agnostic;
+    tk_b200_candidate_t* d_detections;        /* [N][max_detections], (score desc, index asc)             */
+    uint32_t*            d_num_detections;    /* [N]                                                      */
+    uint32_t             restore_src_width, restore_src_height, restore_in_width, restore_in_height;  /* as tk_b200_nms_params_t */
+    void*                d_workspace;         /* needed when max_candidates > 512                         */
+    size_t               workspace_bytes;     /* >= tk_b200_postprocess_fused_workspace_bytes(max_candidates) */
+} tk_b200_post_params_t;
+
+size_t tk_b200_postprocess_fused_workspace_bytes(uint32_t max_candidates);
+TK_NODISCARD tk_error_code_t tk_kernels_postprocess_fused(const tk_b200_post_params_t* params, cudaStream_t stream);
+
 /* Row softmax with fused argmax (either output may be NULL). */
 typedef struct {
     const float* d_input;       /* [rows][cols]           */
@@ -292,6 +319,10 @@ typedef struct {
                                                  only the surviving rows over PCIe (batches under 65536 rows behave as 2); 1 = copy the whole tensor to HBM
                                                  first; 2 = decode reads objectness words and surviving rows in place
                                                  over PCIe (one read request per row)                              */
+    int                   fuse_postprocess;   /* decode + NMS as ONE kernel (tk_kernels_postprocess_fused) that process_device
+                                                 runs on a second stream UNDER the pre-process kernel: 0 = automatic (batches
+                                                 of 32 frames or more), 1 = never (decode_kernel, then nms_kernel, behind the
+                                                 pre-process kernel), 2 = always.  Results are identical either way.   */
 } tk_b200_pipeline_config_t;
 
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out_pipeline, const tk_b200_pipeline_config_t* config);
@@ -391,6 +422,10 @@ unsigned long long tk_b200_launch_count(void);
  * context: bytes = 32 / 64 / 128 sets it, 0 only queries; returns the value in effect. */
 int tk_b200_l2_fetch_granularity(int bytes);   /* kernels enqueued by this library so far */
 int tk_b200_device_count(void);
+/* Debug: register a zeroed DEVICE buffer; the pre-process and post-process kernels then append one 64-byte record per
+ * CTA / per frame ({kernel id << 32 | block, smid << 32 | frame, six %globaltimer stamps}; word 0 of the buffer counts
+ * the records, record i starts at byte 64 (i + 1)).  NULL or 0 bytes turns it off.  Process-wide, not for production. */
+void tk_b200_debug_trace(void* d_buf, size_t bytes);
 
 #ifdef __cplusplus
 }

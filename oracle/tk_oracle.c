@@ -7,11 +7,40 @@
  * Citations are file:line in the reference tree.
  */
 #include "tk_oracle.h"
+/* The ONLY thing the oracle shares with the product is the software exponential (tk_dm_expf / tk_dm_sigmoidf):
+ * glibc's expf and the GPU's differ by ulps, so a bit-exact score contract needs one source for it
+ * (tests/test_post_crosscheck.py holds it against libm within 2 ulp).  Float->int truncation, NaN canonicalisation and
+ * the score order are stated here on their own (or_* below), not taken from that header. */
 #include "../include/tk_b200_detmath.h"
 
+#include <limits.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
+
+/* (int)x of src/vision/tk_object_detector.c:347-350 where the C cast is defined; saturating outside int range and
+ * 0 for NaN, where it is not (the defined behaviour this build fixes on both sides). */
+static int32_t or_trunc_i32(float x) {
+    if (isnan(x)) return 0;
+    const double d = trunc((double)x);
+    if (d >= 2147483647.0) return INT32_MAX;
+    if (d <= -2147483648.0) return INT32_MIN;
+    return (int32_t)d;
+}
+/* an arithmetic NaN has no portable payload: one quiet NaN pattern for all of them */
+static float or_canon_nan(float x) {
+    if (!isnan(x)) return x;
+    const uint32_t q = 0x7fc00000u;
+    float f; memcpy(&f, &q, 4); return f;
+}
+/* IEEE-754 totalOrder of two floats as -1 / 0 / +1 (sign-magnitude integers: -NaN < -inf < ... < -0 < +0 < ... < +NaN) */
+static int or_total_order(float a, float b) {
+    int32_t ia, ib;
+    memcpy(&ia, &a, 4); memcpy(&ib, &b, 4);
+    const int64_t ka = ia < 0 ? -(int64_t)(ia & 0x7fffffff) - 1 : (int64_t)ia;
+    const int64_t kb = ib < 0 ? -(int64_t)(ib & 0x7fffffff) - 1 : (int64_t)ib;
+    return ka < kb ? -1 : (ka > kb ? 1 : 0);
+}
 
 /* ------------------------------------------------------------------------- */
 /* Letterbox geometry, integer-only so host launcher and oracle cannot differ. */
@@ -104,7 +133,7 @@ void oracle_i420_to_rgb8(const uint8_t* i420, uint32_t w, uint32_t h, uint8_t* r
 }
 
 uint16_t oracle_f32_to_f16(float f) {
-    uint32_t x = tk_dm_float_to_bits(f);
+    uint32_t x; memcpy(&x, &f, 4);
     uint32_t sign = (x >> 16) & 0x8000u;
     uint32_t mant = x & 0x007fffffu;
     int32_t exp = (int32_t)((x >> 23) & 0xff);
@@ -149,10 +178,10 @@ uint32_t oracle_decode(const float* logits, uint32_t P, uint32_t C, float thr,
         if (total < cap) {
             oracle_candidate_t* c = &out[total];
             c->index = (int32_t)i;
-            c->x = tk_dm_f2i_trunc(row[0] - row[2] / 2);
-            c->y = tk_dm_f2i_trunc(row[1] - row[3] / 2);
-            c->w = tk_dm_f2i_trunc(row[2]);
-            c->h = tk_dm_f2i_trunc(row[3]);
+            c->x = or_trunc_i32(row[0] - row[2] / 2);
+            c->y = or_trunc_i32(row[1] - row[3] / 2);
+            c->w = or_trunc_i32(row[2]);
+            c->h = or_trunc_i32(row[3]);
             uint32_t best = 0;
             for (uint32_t j = 1; j < C; ++j)
                 if (row[5 + j] > row[5 + best]) best = j;
@@ -170,7 +199,7 @@ uint32_t oracle_decode(const float* logits, uint32_t P, uint32_t C, float thr,
                 cls = tk_dm_expf(row[5 + best] - mx) / sum;
             }
             c->class_id = best;
-            c->confidence = tk_dm_canon_nan(obj * cls);
+            c->confidence = or_canon_nan(obj * cls);
         }
         ++total;
     }
@@ -201,12 +230,12 @@ float oracle_iou(const oracle_candidate_t* a, const oracle_candidate_t* b) {
  * src/gpu/metal/tk_metal_kernels.metal:864-875 (descending score, a box is
  * dropped when IoU with an already-kept box is strictly > thr), restricted to
  * equal class_id (north star) and evaluated sequentially.  Ties: proposal index
- * ascending.  Scores are ordered by tk_dm_float_order_key (IEEE total order). */
+ * ascending.  Scores are ordered by IEEE-754 totalOrder (or_total_order). */
 static int cand_cmp(const void* pa, const void* pb) {
     const oracle_candidate_t* a = (const oracle_candidate_t*)pa;
     const oracle_candidate_t* b = (const oracle_candidate_t*)pb;
-    uint32_t ka = tk_dm_float_order_key(a->confidence), kb = tk_dm_float_order_key(b->confidence);
-    if (ka != kb) return ka > kb ? -1 : 1;
+    const int o = or_total_order(a->confidence, b->confidence);
+    if (o != 0) return -o;                               /* higher score first */
     if (a->index != b->index) return a->index < b->index ? -1 : 1;
     return 0;
 }
@@ -238,10 +267,10 @@ void oracle_restore_coords(oracle_candidate_t* d, uint32_t n, uint32_t src_w, ui
                            uint32_t in_w, uint32_t in_h) {
     float sx = (float)src_w / (float)in_w, sy = (float)src_h / (float)in_h;
     for (uint32_t i = 0; i < n; ++i) {
-        d[i].x = tk_dm_f2i_trunc((float)d[i].x * sx);
-        d[i].y = tk_dm_f2i_trunc((float)d[i].y * sy);
-        d[i].w = tk_dm_f2i_trunc((float)d[i].w * sx);
-        d[i].h = tk_dm_f2i_trunc((float)d[i].h * sy);
+        d[i].x = or_trunc_i32((float)d[i].x * sx);
+        d[i].y = or_trunc_i32((float)d[i].y * sy);
+        d[i].w = or_trunc_i32((float)d[i].w * sx);
+        d[i].h = or_trunc_i32((float)d[i].h * sy);
     }
 }
 

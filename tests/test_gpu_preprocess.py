@@ -92,6 +92,44 @@ def test_half_arithmetic_within_fp16_bar(kind, w, h, ow, oh, fmt):
         assert np.all(np.abs(got - ref) <= F16_TOL + F16_TOL * np.abs(ref))
 
 
+def parity_patterns(w, h, value_pairs):
+    """Frames whose pixel value depends only on (x parity, y parity): every 2x2 neighbourhood is one of the 16 corner
+    combinations of {a, b}, and over the 16 tables every output pixel — i.e. every (xd, yd) the geometry produces —
+    sees all 16 of them (each channel walks the tables with its own offset)."""
+    yy, xx = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
+    sel = ((yy & 1) * 2 + (xx & 1)).astype(np.uint8)
+    for (a, b) in value_pairs:
+        for k in range(16):
+            fr = np.empty((h, w, 3), np.uint8)
+            for c in range(3):
+                fr[..., c] = np.where((((k + 5 * c) % 16) >> sel) & 1, b, a)
+            yield fr
+
+
+@pytest.mark.parametrize("w,h", [(1920, 1080), (640, 480), (3840, 2160)])
+def test_half_arithmetic_adversarial_bound(w, h):
+    """ARITH_HALF under the content that maximises its error terms: 0/255 checkerboards and every other
+    corner combination of {0, 255}, {0, 128}, {127, 128}, {1, 254} at every (x-phase, y-phase) of the map — the xd / yd
+    rounding terms scale with the corner differences, the fp16 rounding of the intermediates with their magnitude —
+    plus single-pixel impulses.  The bar is 1e-2 + 1e-2|ref|; the assertion is HALF of it."""
+    pairs = [(0, 255), (0, 128), (127, 128), (1, 254)]
+    if w == 3840:
+        pairs = pairs[:1]                                   # 4K: the 16 tables of {0, 255} (the oracle takes ~1 s per frame)
+    worst = 0.0
+    frames = list(parity_patterns(w, h, pairs))
+    imp = np.zeros((h, w, 3), np.uint8)
+    imp[::3, ::3] = 255                                     # impulses: isolated 255s, every x / y phase of the 3-pixel grid
+    frames += [imp, 255 - imp]
+    for i in range(0, len(frames), 16):
+        chunk = np.stack(frames[i:i + 16])
+        got = run(chunk, 640, 640, out_dtype=torch.float16, arith=V.ARITH_HALF).astype(np.float32)
+        for j in range(len(chunk)):
+            ref = O.preprocess_rgb8(chunk[j], 640, 640)
+            worst = max(worst, float(np.max(np.abs(got[j] - ref) / (F16_TOL + F16_TOL * np.abs(ref)))))
+    print(f"{w}x{h}: worst err / bar over {len(frames)} adversarial frames = {worst:.3f}")
+    assert worst <= 0.5
+
+
 def test_batch_equals_singles_and_is_deterministic():
     fr = np.stack([synth.rgb_frame(1920, 1080, s) for s in range(5)])
     a = run(fr, 640, 640)

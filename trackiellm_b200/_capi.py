@@ -96,7 +96,18 @@ class PipelineConfig(C.Structure):         # tk_b200_pipeline_config_t
                 ("mean", TkFloat3), ("std_dev", TkFloat3), ("num_proposals", C.c_uint32), ("num_classes", C.c_uint32),
                 ("activation", C.c_int), ("confidence_threshold", C.c_float), ("iou_threshold", C.c_float),
                 ("max_candidates", C.c_uint32), ("max_detections", C.c_uint32), ("class_agnostic", C.c_int),
-                ("restore_coordinates", C.c_int), ("stage_host_logits", C.c_int)]
+                ("restore_coordinates", C.c_int), ("stage_host_logits", C.c_int), ("fuse_postprocess", C.c_int)]
+
+
+class PostParams(C.Structure):             # tk_b200_post_params_t
+    _fields_ = [("d_logits", C.c_void_p), ("num_frames", C.c_uint32), ("num_proposals", C.c_uint32),
+                ("num_classes", C.c_uint32), ("confidence_threshold", C.c_float), ("activation", C.c_int),
+                ("d_candidates", C.c_void_p), ("d_counts", C.c_void_p), ("max_candidates", C.c_uint32),
+                ("iou_threshold", C.c_float), ("max_detections", C.c_uint32), ("class_agnostic", C.c_int),
+                ("d_detections", C.c_void_p), ("d_num_detections", C.c_void_p),
+                ("restore_src_width", C.c_uint32), ("restore_src_height", C.c_uint32),
+                ("restore_in_width", C.c_uint32), ("restore_in_height", C.c_uint32),
+                ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t)]
 
 
 class ArgmaxParams(C.Structure):           # tk_b200_argmax_params_t

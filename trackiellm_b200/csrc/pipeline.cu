@@ -40,7 +40,10 @@ struct tk_b200_pipeline_s {
     size_t frame_bytes, logit_bytes, tensor_bytes;     // per frame
     uint32_t chunk;
     cudaStream_t s_up, s_compute, s_down, s_post;
-    cudaEvent_t ev_post;
+    cudaStream_t s_side;                               // process_device: the fused post-process kernel runs here, under the pre-process kernel
+    cudaEvent_t ev_post, ev_fork, ev_join;
+    int fused;                                         // decode + NMS as ONE co-resident kernel (post.cu)
+    void* d_post_ws; size_t post_ws_bytes;             // its global NMS work area (frames above 512 candidates)
     cudaEvent_t ev_uploaded[tkb::kSlots], ev_computed[tkb::kSlots], ev_downloaded[tkb::kSlots];
     uint8_t* d_frames[tkb::kSlots];                    // [chunk][frame_bytes (+ slack)]
     float*   d_logits[tkb::kSlots];                    // [chunk][P][5+C]
@@ -56,6 +59,7 @@ struct tk_b200_pipeline_s {
     int timing_on;
     uint32_t timing_calls, timing_cap;
     cudaEvent_t* timing_ev;                            // [timing_cap][4]
+    uint8_t* timing_mode;                              // [timing_cap] 0 three kernels in a row, 1 fused post-process behind, 2 beside the pre-process kernel
 };
 
 using namespace tkb;
@@ -78,6 +82,7 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->s_compute) { cudaStreamSynchronize(p->s_compute); }
         if (p->s_down) { cudaStreamSynchronize(p->s_down); }
         if (p->s_post) { cudaStreamSynchronize(p->s_post); }
+        if (p->s_side) { cudaStreamSynchronize(p->s_side); }
         for (int i = 0; i < kSlots; ++i) {
             if (p->d_frames[i]) cudaFree(p->d_frames[i]);
             if (p->d_logits[i]) cudaFree(p->d_logits[i]);
@@ -93,12 +98,16 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->d_obj) cudaFree(p->d_obj);
         if (p->h_obj) cudaFreeHost(p->h_obj);
         for (uint32_t i = 0; p->timing_ev && i < p->timing_cap * 4; ++i) if (p->timing_ev[i]) cudaEventDestroy(p->timing_ev[i]);
-        free(p->timing_ev);
+        free(p->timing_ev); free(p->timing_mode);
         if (p->s_up) cudaStreamDestroy(p->s_up);
         if (p->s_compute) cudaStreamDestroy(p->s_compute);
         if (p->s_down) cudaStreamDestroy(p->s_down);
         if (p->s_post) cudaStreamDestroy(p->s_post);
+        if (p->s_side) cudaStreamDestroy(p->s_side);
         if (p->ev_post) cudaEventDestroy(p->ev_post);
+        if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+        if (p->ev_join) cudaEventDestroy(p->ev_join);
+        if (p->d_post_ws) cudaFree(p->d_post_ws);
         cudaGetLastError();
     }
     delete p;
@@ -137,7 +146,15 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
               cudaStreamCreateWithFlags(&p->s_compute, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&p->s_down, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&p->s_post, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaEventCreateWithFlags(&p->ev_post, cudaEventDisableTiming) == cudaSuccess;
+              cudaEventCreateWithFlags(&p->ev_post, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) == cudaSuccess;
+    if (ok) {
+        // the side stream gets the highest priority: its few small CTAs should be placed before the pre-process grid fills the SMs
+        int lo = 0, hi = 0;
+        if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) { cudaGetLastError(); hi = 0; }
+        ok = cudaStreamCreateWithPriority(&p->s_side, cudaStreamNonBlocking, hi) == cudaSuccess;
+    }
     for (int i = 0; ok && i < kSlots; ++i) {
         ok = cudaEventCreateWithFlags(&p->ev_uploaded[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&p->ev_computed[i], cudaEventDisableTiming) == cudaSuccess &&
@@ -156,6 +173,14 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_counts), mb * sizeof(uint32_t)) == cudaSuccess;
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_dets), mb * p->cfg.max_detections * sizeof(tk_b200_candidate_t)) == cudaSuccess;
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_ndets), mb * sizeof(uint32_t)) == cudaSuccess;
+    // decode + NMS fused into one co-resident kernel: fuse_postprocess 0 = automatic (on for batches that give every
+    // persistent CTA at least ... see run_kernels), 1 = never, 2 = always; TK_B200_POST_FUSED overrides (experiments).
+    p->fused = cfg->fuse_postprocess;
+    if (const char* e = getenv("TK_B200_POST_FUSED")) p->fused = atoi(e);
+    if (ok && p->fused != 1) {
+        p->post_ws_bytes = tk_b200_postprocess_fused_workspace_bytes(p->cfg.max_candidates);
+        if (p->post_ws_bytes) ok = cudaMalloc(&p->d_post_ws, p->post_ws_bytes) == cudaSuccess;
+    }
     if (!ok) {
         tk_error_set_detail("pipeline buffers: %s", cudaGetErrorString(cudaGetLastError()));
         tk_b200_pipeline_destroy(&p);
@@ -189,22 +214,75 @@ static tk_b200_preprocess_batch_params_t pre_params(const tk_b200_pipeline_t* p,
     return b;
 }
 
-// The three launches for `n` frames whose inputs are in HBM.
+// Whether `n` frames take the fused co-resident post-process kernel: one persistent 256-thread CTA works a whole frame
+// (~70 us of latency-bound work), which pays when there are frames enough to spread over the SMs and a pre-process
+// kernel long enough to hide it under; a handful of frames is faster through the 8-CTA-per-frame decode_kernel.
+static bool use_fused(const tk_b200_pipeline_t* p, uint32_t n) {
+    (void)n;
+    return p->fused == 2;        // automatic stays off until the co-resident step beats the three kernels in a row
+}
+
+// The launches for `n` frames whose inputs are in HBM: the pre-process kernel on `st`, and
+//   separate : decode_kernel, nms_kernel behind it on `st` (3 launches);
+//   fused    : post_kernel (decode + NMS per frame) on the side stream, forked off `st` before the pre-process launch
+//              and joined after it (2 launches): the two kernels share no data and are sized to be resident together
+//              (post.cu), so the post-process runs UNDER the pre-process kernel.
+// tev (stage timing): [0] start, [1] pre-process done, [2] decode done (fused: post_kernel done, recorded on the side
+// stream), [3] end.
 static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits, uint32_t n,
                                    void* d_tensor, tk_b200_candidate_t* d_cands, uint32_t* d_counts,
                                    tk_b200_candidate_t* d_dets, uint32_t* d_ndets, cudaStream_t st,
-                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr) {
+                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr, uint8_t* out_fused = nullptr) {
     const tk_b200_pipeline_config_t& c = p->cfg;
     tk_error_code_t rc;
+    if (out_fused) *out_fused = 0;
+    if (d_logits && (!d_dets || !d_ndets)) return TK_ERROR_INVALID_ARGUMENT;
+    if (d_frames && !d_tensor) return TK_ERROR_INVALID_ARGUMENT;
+    if (d_logits && c.restore_coordinates && c.resize_mode != TK_B200_RESIZE_STRETCH)
+        return TK_ERROR_NOT_IMPLEMENTED;   // a letterboxed tensor would also need the pad offsets, which the reference
+                                           // never defines (convert_to_original_coordinates is empty)
+    const bool fused = d_logits && use_fused(p, n);
+    bool fork = fused && d_frames;                             // something to run beside
     if (tev) cudaEventRecord(tev[0], st);
+    if (fused) {
+        tk_b200_post_params_t q{};
+        q.d_logits = d_logits; q.num_frames = n; q.num_proposals = c.num_proposals; q.num_classes = c.num_classes;
+        q.confidence_threshold = c.confidence_threshold; q.activation = c.activation;
+        q.d_candidates = d_cands; q.d_counts = d_counts; q.max_candidates = c.max_candidates;
+        q.iou_threshold = c.iou_threshold; q.max_detections = c.max_detections; q.class_agnostic = c.class_agnostic;
+        q.d_detections = d_dets; q.d_num_detections = d_ndets;
+        if (c.restore_coordinates) {
+            q.restore_src_width = c.input_width; q.restore_src_height = c.input_height;
+            q.restore_in_width = c.tensor_width; q.restore_in_height = c.tensor_height;
+        }
+        q.d_workspace = p->d_post_ws; q.workspace_bytes = p->post_ws_bytes;
+        cudaStream_t ps = fork ? p->s_side : st;
+        if (fork) {
+            TK_CUDA_TRY(cudaEventRecord(p->ev_fork, st), TK_ERROR_GPU_CUDA_ERROR);
+            TK_CUDA_TRY(cudaStreamWaitEvent(ps, p->ev_fork, 0), TK_ERROR_GPU_CUDA_ERROR);
+        }
+        rc = postprocess_fused_packed(&q, d_obj, ps);
+        if (rc == TK_ERROR_NOT_IMPLEMENTED) {
+            fork = false;                                      // head shapes the fused kernel's 25 KB do not hold: the two-kernel path below
+        } else {
+            if (rc != TK_SUCCESS) return rc;
+            if (fork) {
+                if (tev) cudaEventRecord(tev[2], ps);
+                TK_CUDA_TRY(cudaEventRecord(p->ev_join, ps), TK_ERROR_GPU_CUDA_ERROR);
+            } else if (tev) {
+                cudaEventRecord(tev[2], ps);
+            }
+            if (out_fused) *out_fused = fork ? 2 : 1;
+            d_logits = nullptr;                                // done (or in flight on the side stream)
+        }
+    }
     if (d_frames) {
-        if (!d_tensor) return TK_ERROR_INVALID_ARGUMENT;
         const tk_b200_preprocess_batch_params_t b = pre_params(p, d_frames, n, d_tensor);
         if ((rc = tk_b200_preprocess_batch(&b, st)) != TK_SUCCESS) return rc;
     }
     if (tev) cudaEventRecord(tev[1], st);
+    if (fork) TK_CUDA_TRY(cudaStreamWaitEvent(st, p->ev_join, 0), TK_ERROR_GPU_CUDA_ERROR);
     if (d_logits) {
-        if (!d_dets || !d_ndets) return TK_ERROR_INVALID_ARGUMENT;
         tk_b200_decode_params_t d{};
         d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
         d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
@@ -216,14 +294,11 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
         m.iou_threshold = c.iou_threshold; m.max_detections = c.max_detections; m.class_agnostic = c.class_agnostic;
         m.d_detections = d_dets; m.d_num_detections = d_ndets;
         if (c.restore_coordinates) {
-            // Stretch inverse; a letterboxed tensor would also need the pad offsets, which
-            // the reference never defines (convert_to_original_coordinates is empty).
-            if (c.resize_mode != TK_B200_RESIZE_STRETCH) return TK_ERROR_NOT_IMPLEMENTED;
             m.restore_src_width = c.input_width; m.restore_src_height = c.input_height;
             m.restore_in_width = c.tensor_width; m.restore_in_height = c.tensor_height;
         }
         if ((rc = tk_kernels_nms_classwise(&m, st)) != TK_SUCCESS) return rc;
-    } else if (tev) {
+    } else if (tev && !fused) {
         cudaEventRecord(tev[2], st);
     }
     if (tev) cudaEventRecord(tev[3], st);
@@ -239,8 +314,12 @@ extern "C" tk_error_code_t tk_b200_pipeline_process_device(tk_b200_pipeline_t* p
     DevScope scope(p->cfg.device_id);
     if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
     cudaEvent_t* tev = nullptr;
-    if (p->timing_on && p->timing_calls < p->timing_cap) tev = p->timing_ev + 4 * (size_t)p->timing_calls++;
-    return run_kernels(p, d_frames, d_logits, n, d_tensor, p->d_cands, p->d_counts, d_dets, d_ndets, stream, tev);
+    uint8_t* mode = nullptr;
+    if (p->timing_on && p->timing_calls < p->timing_cap) {
+        mode = p->timing_mode + p->timing_calls;
+        tev = p->timing_ev + 4 * (size_t)p->timing_calls++;
+    }
+    return run_kernels(p, d_frames, d_logits, n, d_tensor, p->d_cands, p->d_counts, d_dets, d_ndets, stream, tev, nullptr, mode);
 }
 
 // Stage timing of process_device with CUDA events on the caller's stream.
@@ -253,10 +332,16 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_timing(tk_b200_pipeline_t* p, 
     if (max_calls == 0) return TK_SUCCESS;
     if (max_calls > p->timing_cap) {
         cudaEvent_t* ev = static_cast<cudaEvent_t*>(calloc((size_t)max_calls * 4, sizeof(cudaEvent_t)));
-        if (!ev) return TK_ERROR_OUT_OF_MEMORY;
+        uint8_t* md = static_cast<uint8_t*>(calloc(max_calls, 1));
+        if (!ev || !md) { free(ev); free(md); return TK_ERROR_OUT_OF_MEMORY; }
+        free(p->timing_mode); p->timing_mode = md;
         for (uint32_t i = 0; i < max_calls * 4; ++i) {
             if (i < p->timing_cap * 4) ev[i] = p->timing_ev[i];
-            else if (cudaEventCreate(&ev[i]) != cudaSuccess) { cudaGetLastError(); free(ev); return TK_ERROR_GPU_CUDA_ERROR; }
+            else if (cudaEventCreate(&ev[i]) != cudaSuccess) {
+                // keep what exists: the old events stay owned by the old table
+                for (uint32_t j = p->timing_cap * 4; j < i; ++j) cudaEventDestroy(ev[j]);
+                cudaGetLastError(); free(ev); return TK_ERROR_GPU_CUDA_ERROR;
+            }
         }
         free(p->timing_ev);
         p->timing_ev = ev; p->timing_cap = max_calls;
@@ -265,8 +350,9 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_timing(tk_b200_pipeline_t* p, 
     return TK_SUCCESS;
 }
 
-// Sums of the recorded stage durations (ms): [0] pre-process, [1] decode, [2] NMS;
-// *out_calls = calls recorded.  Waits for the recorded events to complete.
+// Sums of the recorded stage durations (ms): [0] pre-process, [1] decode, [2] NMS; *out_calls = calls recorded.
+// Calls that ran the fused post-process kernel: [1] = post_kernel (decode + NMS) from the fork to its end — it runs
+// beside the pre-process kernel, so [0] + [1] exceeds the step — and [2] = 0.  Waits for the recorded events.
 extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, double ms_sum[3], uint32_t* out_calls) {
     if (!p || !ms_sum || !out_calls) return TK_ERROR_INVALID_ARGUMENT;
     DevScope scope(p->cfg.device_id);
@@ -276,6 +362,14 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
     for (uint32_t c = 0; c < p->timing_calls; ++c) {
         cudaEvent_t* e = p->timing_ev + 4 * (size_t)c;
         TK_CUDA_TRY(cudaEventSynchronize(e[3]), TK_ERROR_GPU_SYNCHRONIZATION_FAILED);
+        if (p->timing_mode[c] != 0) {
+            float a = 0.0f, b = 0.0f;
+            TK_CUDA_TRY(cudaEventSynchronize(e[2]), TK_ERROR_GPU_SYNCHRONIZATION_FAILED);
+            if (p->timing_mode[c] == 2) TK_CUDA_TRY(cudaEventElapsedTime(&a, e[0], e[1]), TK_ERROR_GPU_CUDA_ERROR);
+            TK_CUDA_TRY(cudaEventElapsedTime(&b, e[0], e[2]), TK_ERROR_GPU_CUDA_ERROR);
+            ms_sum[0] += (double)a; ms_sum[1] += (double)b;
+            continue;
+        }
         for (int s = 0; s < 3; ++s) {
             float ms = 0.0f;
             TK_CUDA_TRY(cudaEventElapsedTime(&ms, e[s], e[s + 1]), TK_ERROR_GPU_CUDA_ERROR);

@@ -56,6 +56,7 @@ struct PreK {
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
     uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
     float one;              // 1.0f at run time (see sum2)
+    TraceBuf trace;         // debug: per-CTA record (tk_b200_debug_trace), buf == nullptr when off
 };
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
@@ -225,7 +226,7 @@ __device__ __forceinline__ void warp_copy_unaligned(uint8_t* dst, const uint8_t*
 // There is no CTA-wide barrier after set-up.
 // HALF arithmetic (fp16 output, RGB8 / RGBA8): the 2x2 neighbourhood as half2 {R,G} and {B,B}
 // pairs, 0x6400 | byte == 1024 + byte exactly, differences exact, lerps and the
-// normalisation in HFMA2 — half the math instructions of the fp32 lerp.
+// normalisation in HFMA2 — half the math instructions of the fp32 lerp.  Error bound: DESIGN.md §3.
 template <int FMT>
 __device__ __forceinline__ void fetch_pairs_half(const uint8_t* row, int xb, uint32_t& l_rg, uint32_t& l_bb,
                                                  uint32_t& r_rg, uint32_t& r_bb) {
@@ -247,9 +248,11 @@ __device__ __forceinline__ void fetch_pairs_half(const uint8_t* row, int xb, uin
 __device__ __forceinline__ __half2 as_h2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
 __device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 __device__ __forceinline__ __half2 lerp_pair_half(uint32_t tl, uint32_t tr, uint32_t bl, uint32_t br, __half2 xd2, __half2 yd2) {
-    const __half2 k1024 = as_h2(0x64006400u);
-    const __half2 top = __hfma2(xd2, __hsub2(as_h2(tr), as_h2(tl)), __hsub2(as_h2(tl), k1024));
-    const __half2 bot = __hfma2(xd2, __hsub2(as_h2(br), as_h2(bl)), __hsub2(as_h2(bl), k1024));
+    // 1152 = 1024 + 128: the lerp runs on CENTRED values (byte - 128, |v| <= 128), which halves the fp16 rounding step of
+    // every intermediate against values up to 255; the +128 is folded into the bias constant on the host.
+    const __half2 k1152 = as_h2(0x64806480u);
+    const __half2 top = __hfma2(xd2, __hsub2(as_h2(tr), as_h2(tl)), __hsub2(as_h2(tl), k1152));
+    const __half2 bot = __hfma2(xd2, __hsub2(as_h2(br), as_h2(bl)), __hsub2(as_h2(bl), k1152));
     return __hfma2(yd2, __hsub2(bot, top), top);
 }
 
@@ -270,6 +273,8 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
     const uint32_t tid = threadIdx.x;
     const uint32_t ncons = p.tx * p.ty;
     const uint32_t S = 1u << p.s_log2, smask = S - 1;
+    unsigned long long t_trace[2];
+    if (p.trace.buf && tid == 0) t_trace[0] = gtimer();
 
     if (tid == 0) {
         for (uint32_t s = 0; s < S; ++s) mbar_init(&full[s], 1);
@@ -410,8 +415,8 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
             for (uint32_t q = cx; q < Q; q += p.tx) {
                 if constexpr (AR == AR_HALF) {
                     const __half2 yd2 = __float2half2_rn(yd);
-                    const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                    const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                    const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                    const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
                     uint32_t org[4], obb[4];
                     if (vin) {
                         const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
@@ -510,6 +515,7 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
         seq_base += (uint32_t)nrows;
     }
     pass_to(0xffffffffu);                        // done: nothing this warp could still read
+    if (p.trace.buf && tid == 0) { t_trace[1] = gtimer(); trace_put(p.trace, 1u, blockIdx.x, (uint32_t)(g1 - g0), t_trace, 2); }
     // Possibly launched early behind an unrelated kernel (see launch_variant): complete only after it has.
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
@@ -553,6 +559,9 @@ template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 static tk_error_code_t launch_variant(const PreK& k, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
     auto kern = preprocess_kernel<FMT, F16, AR, LBOX, TMA>;
     TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    // Largest shared-memory carve-out, like post_kernel (post.cu), which the pipeline runs beside this kernel: with one
+    // L1 / shared split for both, an SM never drains to reconfigure between them.
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     // Launched as a programmatic dependent (TK_B200_PDL_PRE=0 turns it off).  The kernel reads only the
     // caller's frames, so behind a kernel that has announced (griddepcontrol.launch_dependents) that its
     // dependents need not wait for it — nms_kernel of the previous step, which keeps 64 of 148 SMs busy at the
@@ -662,6 +671,7 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     k.y_ratio = ((float)k.src_h - 1.0f) / (float)k.new_h;
     k.swap_rb = bgr ? 1u : 0u;
     k.one = 1.0f;
+    k.trace = trace_target();
     for (int c = 0; c < 3; ++c) {
         // constants are indexed by SOURCE channel; BGR byte c is tensor channel 2 - c
         const int tc = bgr ? 2 - c : c;
@@ -676,8 +686,15 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
             __half2 v = __floats2half2_rn(lo, hi);
             uint32_t u; memcpy(&u, &v, 4); return u;
         };
-        k.h_scale_rg = h2(k.fscale[0], k.fscale[1]); k.h_bias_rg = h2(k.fbias[0], k.fbias[1]);
-        k.h_scale_bb = h2(k.fscale[2], k.fscale[2]); k.h_bias_bb = h2(k.fbias[2], k.fbias[2]);
+        // HALF works on byte - 128: bias' = -mean/std + 128/(255 std), rounded once from double
+        float hb[3];
+        for (int c = 0; c < 3; ++c) {
+            const int tc = bgr ? 2 - c : c;
+            const double mu = (&prm->mean.x)[tc], sd = (&prm->std_dev.x)[tc];
+            hb[c] = (float)(-mu / sd + 128.0 / (255.0 * sd));
+        }
+        k.h_scale_rg = h2(k.fscale[0], k.fscale[1]); k.h_bias_rg = h2(hb[0], hb[1]);
+        k.h_scale_bb = h2(k.fscale[2], k.fscale[2]); k.h_bias_bb = h2(hb[2], hb[2]);
     }
     unsigned long long frame_bytes = (unsigned long long)k.src_stride * k.src_h;
     if (fmt == FMT_I420) {

@@ -13,6 +13,10 @@ static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
+static std::atomic<unsigned long long*> g_trace_buf{nullptr};
+static std::atomic<uint32_t> g_trace_cap{0};
+TraceBuf trace_target() { return TraceBuf{g_trace_buf.load(std::memory_order_relaxed), g_trace_cap.load(std::memory_order_relaxed)}; }
+
 static DeviceInfo g_info[64];
 static int g_info_state[64];   // 0 unknown, 1 ok, -1 bad
 static std::mutex g_info_mu;
@@ -104,6 +108,13 @@ extern "C" int tk_b200_l2_fetch_granularity(int bytes) {
     size_t v = 0;
     if (cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity) != cudaSuccess) { cudaGetLastError(); return -1; }
     return (int)v;
+}
+
+// Debug trace target: a DEVICE buffer of `bytes` (>= 128) that the caller zeroes and reads back; NULL / 0 turns it off.
+extern "C" void tk_b200_debug_trace(void* d_buf, size_t bytes) {
+    const uint32_t cap = (d_buf && bytes >= 128) ? (uint32_t)((bytes - 64) / 64) : 0u;
+    tkb::g_trace_cap.store(cap, std::memory_order_relaxed);
+    tkb::g_trace_buf.store(cap ? static_cast<unsigned long long*>(d_buf) : nullptr, std::memory_order_relaxed);
 }
 
 extern "C" unsigned long long tk_b200_launch_count(void) { return tkb::launch_count(); }

@@ -37,9 +37,19 @@ bool preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t* prm
 // page-locked host memory: pass 1 reads HBM, only the surviving rows cross PCIe.
 tk_error_code_t decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream);
 
+// post.cu: tk_kernels_postprocess_fused with the objectness column supplied densely (see decode_detections_packed).
+tk_error_code_t postprocess_fused_packed(const tk_b200_post_params_t* p, const float* d_objectness, cudaStream_t stream);
+
 // Number of kernels this library has enqueued (every launcher goes through
 // launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
 void count_launch();
+
+// Debug trace (tk_b200_debug_trace): when a device buffer is registered, the pre-process and post-process kernels
+// append one 64-byte record per CTA (pre-process) or per frame (post-process) — SM id and %globaltimer stamps — which
+// is how the co-residency timeline in profiles/ was taken (there is no nsys in this image).  One predicated store per
+// CTA when enabled; nothing when the pointer is null.
+struct TraceBuf { unsigned long long* buf; uint32_t cap; };   // buf[0]: records written; record i at buf[8 + 8 i]
+TraceBuf trace_target();
 
 // Post-launch check shared by every launcher (reference convention:
 // cudaGetLastError after enqueue, src/gpu/cuda/tk_cuda_kernels.cu:297-300).
@@ -54,6 +64,19 @@ inline tk_error_code_t launch_status(const char* what) {
 }
 
 #ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
+}
+__device__ __forceinline__ uint32_t my_smid() { uint32_t s; asm volatile("mov.u32 %0, %%smid;" : "=r"(s)); return s; }
+// record: {kernel id << 32 | a, smid << 32 | b, t[0..5]}
+__device__ __forceinline__ void trace_put(const TraceBuf& t, uint32_t kid, uint32_t a, uint32_t b, const unsigned long long* ts, int nts) {
+    const unsigned long long i = atomicAdd(t.buf, 1ull);
+    if (i >= t.cap) return;
+    unsigned long long* r = t.buf + 8 + 8 * i;
+    r[0] = ((unsigned long long)kid << 32) | a;
+    r[1] = ((unsigned long long)my_smid() << 32) | b;
+    for (int j = 0; j < 6; ++j) r[2 + j] = j < nts ? ts[j] : 0ull;
+}
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }

@@ -62,7 +62,7 @@ def preprocess_batch(frames: torch.Tensor, out_w: int, out_h: int, *, width: int
     pitch = frames.stride(0) * frames.element_size()
     f16 = out_dtype == torch.float16
     if arith is None:
-        arith = ARITH_HALF if f16 else ARITH_EXACT     # HALF falls back to FAST inside the library for I420
+        arith = ARITH_EXACT                            # the reference's arithmetic; HALF / FAST are opt-in
     if out is None:
         out = torch.empty((n, 3, out_h, out_w), dtype=out_dtype, device=frames.device)
     p = capi.PreprocessBatchParams(
@@ -140,6 +140,32 @@ def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float
     with torch.cuda.device(candidates.device):
         capi.check(capi.lib().tk_kernels_nms_classwise(C.byref(prm), _stream()), "tk_kernels_nms_classwise")
     return detections, num_detections
+
+
+def postprocess_fused(logits: torch.Tensor, conf_thr: float, iou_thr: float, max_detections: int, *, act: int = ACT_RAW,
+                      max_candidates: int = 4096, class_agnostic: bool = False,
+                      restore: tuple[int, int, int, int] | None = None):
+    """tk_kernels_postprocess_fused: decode + class-wise NMS per frame in one kernel.
+    -> (candidates, counts, detections, num_detections) as decode_detections / nms_classwise return them."""
+    _require_cuda(logits, "logits")
+    n, p, l = logits.shape
+    dev = logits.device
+    cands = torch.empty((n, max_candidates, CAND_WORDS), dtype=torch.int32, device=dev)
+    counts = torch.empty((n,), dtype=torch.int32, device=dev)
+    dets = torch.empty((n, max_detections, CAND_WORDS), dtype=torch.int32, device=dev)
+    ndets = torch.empty((n,), dtype=torch.int32, device=dev)
+    L = capi.lib()
+    L.tk_b200_postprocess_fused_workspace_bytes.restype = C.c_size_t
+    with torch.cuda.device(dev):
+        need = int(L.tk_b200_postprocess_fused_workspace_bytes(C.c_uint32(max_candidates)))
+        ws = torch.empty((need,), dtype=torch.uint8, device=dev) if need else None
+        prm = capi.PostParams(logits.data_ptr(), n, p, l - 5, conf_thr, act, cands.data_ptr(), counts.data_ptr(),
+                              max_candidates, iou_thr, max_detections, int(class_agnostic), dets.data_ptr(),
+                              ndets.data_ptr(), *(restore or (0, 0, 0, 0)), ws.data_ptr() if ws is not None else None, need)
+        capi.check(L.tk_kernels_postprocess_fused(C.byref(prm), _stream()), "tk_kernels_postprocess_fused")
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream())
+    return cands, counts, dets, ndets
 
 
 def candidates_to_numpy(cands: torch.Tensor, counts: torch.Tensor) -> list[np.ndarray]:
@@ -361,10 +387,10 @@ class Pipeline:
                  mean=IMAGENET_MEAN, std=IMAGENET_STD, num_proposals: int = 25200, num_classes: int = 80,
                  act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
                  max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False,
-                 stage_host_logits: int = 0):
+                 stage_host_logits: int = 0, fuse_postprocess: int = 0):
         f16 = out_dtype == torch.float16
         if arith is None:
-            arith = ARITH_HALF if f16 else ARITH_EXACT
+            arith = ARITH_EXACT                        # the reference's arithmetic; HALF / FAST are opt-in
         self.cfg = capi.PipelineConfig(
             device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, input_width=width,
             input_height=height, input_stride_bytes=stride, input_format=fmt, tensor_width=tensor_w,
@@ -372,7 +398,8 @@ class Pipeline:
             pad_value=pad_value, mean=_f3(mean), std_dev=_f3(std), num_proposals=num_proposals,
             num_classes=num_classes, activation=act, confidence_threshold=conf_thr, iou_threshold=iou_thr,
             max_candidates=max_candidates, max_detections=max_detections, class_agnostic=int(class_agnostic),
-            restore_coordinates=int(restore_coordinates), stage_host_logits=int(stage_host_logits))
+            restore_coordinates=int(restore_coordinates), stage_host_logits=int(stage_host_logits),
+            fuse_postprocess=int(fuse_postprocess))
         self.out_dtype = out_dtype
         self.device = torch.device("cuda", device_id)
         self._h = C.c_void_p()
