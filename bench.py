@@ -769,8 +769,9 @@ def main() -> None:
     ap.add_argument("--only-headline", action="store_true", help="skip workloads / sweep / detect latency (experiments)")
     ap.add_argument("--arith", default="exact", choices=["exact", "half", "fast"],
                     help="pre-process arithmetic of the headline (default: the reference's, bit-exact)")
-    ap.add_argument("--fuse", type=int, default=0, choices=[0, 1, 2],
-                    help="decode + NMS as one co-resident kernel beside the pre-process kernel: 0 library default, 1 off, 2 on")
+    ap.add_argument("--fuse", type=int, default=0, choices=[0, 1, 2, 3],
+                    help="post-process form: 0 / 1 decode_kernel then nms_kernel (library default), 2 one persistent co-resident "
+                         "kernel beside the pre-process kernel, 3 one cluster-fused kernel behind it")
     ap.add_argument("--logits-mode", type=int, default=0, choices=[0, 1, 2],
                     help="e2e, host logits: 0 objectness column packed on the host + surviving rows in place (default), "
                          "1 whole tensor copied to HBM, 2 objectness and rows read in place over PCIe")

@@ -178,11 +178,13 @@ typedef struct {
 
 TK_NODISCARD tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* params, cudaStream_t stream);
 
-/* Decode + class-wise NMS of whole frames in ONE kernel (decode_kernel + nms_kernel fused per frame; completes
- * src/vision/tk_object_detector.c:343-357 in one pass).  Cut to 256 threads, <= 32 registers and 25 KB of shared
- * memory per CTA so that it can be RESIDENT BESIDE another kernel (the pipeline runs it on a second stream under
- * the pre-process kernel).  Same results, bit for bit, as tk_kernels_decode_detections followed by
- * tk_kernels_nms_classwise; d_candidates / d_counts receive the intermediate list exactly as decode leaves it.
+/* Decode + class-wise NMS of whole frames in ONE kernel (completes src/vision/tk_object_detector.c:343-357 in one
+ * pass).  Same results, bit for bit, as tk_kernels_decode_detections followed by tk_kernels_nms_classwise;
+ * d_candidates / d_counts receive the intermediate list exactly as decode leaves it.  Two layouts:
+ *   0  a thread-block cluster of 8 CTAs per frame decodes it, then the cluster's first CTA runs the frame's NMS at once
+ *      (one launch, no gap, the NMS of early frames hides under the decode of late ones);
+ *   1  one persistent 256-thread CTA (<= 32 registers, 25 KB of shared memory) works whole frames — cut to be
+ *      RESIDENT BESIDE another kernel's CTAs on a second stream (measured in DESIGN.md §9; not the default).
  * Frames with more than 512 candidates run their NMS through d_workspace (global memory): slower, same result. */
 typedef struct {
     const float*         d_logits;            /* [N][P][5+C] fp32 row-major                               */
@@ -191,7 +193,7 @@ typedef struct {
     tk_b200_activation_e activation;
     tk_b200_candidate_t* d_candidates;        /* [N][max_candidates]                                      */
     uint32_t*            d_counts;            /* [N] rows passing the threshold (may exceed the cap)      */
-    uint32_t             max_candidates;      /* <= 4096                                                  */
+    uint32_t             max_candidates;      /* any (no 4096 limit: larger lists sort in d_workspace)    */
     float                iou_threshold;
     uint32_t             max_detections;
     int                  class_agnostic;
@@ -199,10 +201,11 @@ typedef struct {
     uint32_t*            d_num_detections;    /* [N]                                                      */
     uint32_t             restore_src_width, restore_src_height, restore_in_width, restore_in_height;  /* as tk_b200_nms_params_t */
     void*                d_workspace;         /* needed when max_candidates > 512                         */
-    size_t               workspace_bytes;     /* >= tk_b200_postprocess_fused_workspace_bytes(max_candidates) */
+    size_t               workspace_bytes;     /* >= tk_b200_postprocess_fused_workspace_bytes(max_candidates, num_frames, layout) */
+    int                  layout;              /* 0 cluster per frame, 1 persistent co-resident CTAs       */
 } tk_b200_post_params_t;
 
-size_t tk_b200_postprocess_fused_workspace_bytes(uint32_t max_candidates);
+size_t tk_b200_postprocess_fused_workspace_bytes(uint32_t max_candidates, uint32_t num_frames, int layout);
 TK_NODISCARD tk_error_code_t tk_kernels_postprocess_fused(const tk_b200_post_params_t* params, cudaStream_t stream);
 
 /* Row softmax with fused argmax (either output may be NULL). */
@@ -319,10 +322,12 @@ typedef struct {
                                                  only the surviving rows over PCIe (batches under 65536 rows behave as 2); 1 = copy the whole tensor to HBM
                                                  first; 2 = decode reads objectness words and surviving rows in place
                                                  over PCIe (one read request per row)                              */
-    int                   fuse_postprocess;   /* decode + NMS as ONE kernel (tk_kernels_postprocess_fused) that process_device
-                                                 runs on a second stream UNDER the pre-process kernel: 0 = automatic (batches
-                                                 of 32 frames or more), 1 = never (decode_kernel, then nms_kernel, behind the
-                                                 pre-process kernel), 2 = always.  Results are identical either way.   */
+    int                   fuse_postprocess;   /* 0 / 1 = decode_kernel, then nms_kernel, behind the pre-process kernel (the
+                                                 default: fastest as measured); decode + NMS as ONE kernel
+                                                 (tk_kernels_postprocess_fused): 3 = a cluster of 8 CTAs per frame decodes it
+                                                 and then runs its NMS, 2 = the persistent co-resident form on a second stream
+                                                 BESIDE the pre-process kernel.  Both measured slower, kept
+                                                 selectable; results are identical in every mode.                          */
 } tk_b200_pipeline_config_t;
 
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out_pipeline, const tk_b200_pipeline_config_t* config);
@@ -330,7 +335,17 @@ void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pipeline);
 /* src/vision/tk_object_detector.h:166 (tk_object_detector_update_thresholds) */
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_update_thresholds(tk_b200_pipeline_t* pipeline, float confidence_threshold, float iou_threshold);
 
-/* DEVICE-resident inputs and outputs; asynchronous on `stream` (3 launches).
+/* Candidate-cap report.  max_candidates is a cap the CALLER chooses (the reference keeps every row over the threshold,
+ * src/vision/tk_object_detector.c:339-355; the reference-typed entry points tk_object_detector_detect and
+ * tk_b200_postprocess_detections therefore never truncate: a frame over the kernels' 4096 is done again uncapped).
+ * A frame of a pipeline call with more rows over the threshold than max_candidates is cut to the first
+ * max_candidates rows by proposal index before NMS; these two calls say when that happened.
+ *   _candidate_overflow: after process_host[_frames] — frames of that call that were cut, largest row count seen
+ *   _candidate_counts_device_ptr: process_device — u32[n] rows over the threshold per frame (device, stream-ordered) */
+TK_NODISCARD tk_error_code_t tk_b200_pipeline_candidate_overflow(tk_b200_pipeline_t* pipeline, uint32_t* out_frames, uint32_t* out_max_count);
+const uint32_t* tk_b200_pipeline_candidate_counts_device_ptr(tk_b200_pipeline_t* pipeline);
+
+/* DEVICE-resident inputs and outputs; asynchronous on `stream` (3 launches; 2 with a fused post-process).
  * d_frames [n][frame bytes], d_logits [n][P][5+C] f32, d_tensor [n][3][H][W],
  * d_detections [n][max_detections], d_num_detections [n]. */
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_device(
@@ -356,7 +371,9 @@ TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_host(
     void* h_tensor, tk_b200_candidate_t* h_detections, uint32_t* h_num_detections);
 
 /* As process_host, but the logits are already on the device (where a co-located
- * detector leaves them). */
+ * detector leaves them).  d_logits must be COMPLETE and visible to the
+ * device before the call (synchronise the stream that wrote them, or record an event and
+ * wait for it): the call reads them on the pipeline's own streams. */
 TK_NODISCARD tk_error_code_t tk_b200_pipeline_process_host_frames(
     tk_b200_pipeline_t* pipeline, const void* h_frames, const float* d_logits, uint32_t num_frames,
     void* h_tensor, tk_b200_candidate_t* h_detections, uint32_t* h_num_detections);
@@ -371,6 +388,35 @@ TK_NODISCARD tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* pi
 void*  tk_b200_pipeline_tensor_device_ptr(tk_b200_pipeline_t* pipeline);
 size_t tk_b200_pipeline_frame_bytes(const tk_b200_pipeline_t* pipeline);
 size_t tk_b200_pipeline_tensor_bytes(const tk_b200_pipeline_t* pipeline);   /* per frame */
+
+/* ------------------------------------------------------------------------ */
+/* Multi-device harness: ONE process, one host thread + one        */
+/* pipeline (own streams) per device, frames sharded by contiguous block        */
+/* [g*n/G, (g+1)*n/G), no exchange step and no collective: every device writes  */
+/* its block's outputs straight into the caller's host arrays.  The reference    */
+/* has one device per dispatcher and no multi-device form                        */
+/* (src/gpu/cuda/tk_cuda_dispatch.h:47-49, tk_cuda_dispatch.cu:163-247).         */
+/* ------------------------------------------------------------------------ */
+typedef struct tk_b200_shard_s tk_b200_shard_t;
+
+/* device_ids[num_devices] (an id may repeat); config as tk_b200_pipeline_create with device_id ignored and max_batch =
+ * the WHOLE job's batch.  The host threads are bound to the CPUs of their GPU's NUMA node when sysfs names them. */
+TK_NODISCARD tk_error_code_t tk_b200_shard_create(tk_b200_shard_t** out_shard, const int* device_ids, uint32_t num_devices,
+                                                  const tk_b200_pipeline_config_t* config);
+void tk_b200_shard_destroy(tk_b200_shard_t** shard);
+uint32_t tk_b200_shard_num_devices(const tk_b200_shard_t* shard);
+void tk_b200_shard_block(uint32_t num_frames, uint32_t device_index, uint32_t num_devices, uint32_t* out_first, uint32_t* out_count);
+TK_NODISCARD tk_error_code_t tk_b200_shard_update_thresholds(tk_b200_shard_t* shard, float confidence_threshold, float iou_threshold);
+/* Buffers of the whole job, laid out as for tk_b200_pipeline_process_host; blocks until every device is done. */
+TK_NODISCARD tk_error_code_t tk_b200_shard_process_host(tk_b200_shard_t* shard, const void* h_frames, const float* h_logits,
+                                                        uint32_t num_frames, void* h_tensor, tk_b200_candidate_t* h_detections,
+                                                        uint32_t* h_num_detections);
+TK_NODISCARD tk_error_code_t tk_b200_shard_candidate_overflow(tk_b200_shard_t* shard, uint32_t* out_frames, uint32_t* out_max_count);
+/* Final host gather: padded per-frame lists -> flat list in frame order + offsets[n + 1] (prefix sum of the counts).
+ * out_flat may be NULL to size it. */
+TK_NODISCARD tk_error_code_t tk_b200_shard_gather(const tk_b200_candidate_t* h_detections, const uint32_t* h_num_detections,
+                                                  uint32_t num_frames, uint32_t max_detections, tk_b200_candidate_t* out_flat,
+                                                  uint64_t* out_offsets);
 
 /* Single frame, reference result type: completes postprocess_detections
  * (src/vision/tk_object_detector.c:303-368) for a HOST logit tensor
@@ -410,6 +456,12 @@ void*        tk_b200_buffer_device_ptr(tk_gpu_buffer_t buffer);
 size_t       tk_b200_buffer_size(tk_gpu_buffer_t buffer);
 cudaStream_t tk_b200_dispatch_stream(tk_cuda_dispatcher_t* dispatcher);
 int          tk_b200_dispatch_device(tk_cuda_dispatcher_t* dispatcher);
+
+/* The host-pointer entry points (tk_preprocessor_resize_and_normalize_to_chw, tk_classify_*,
+ * tk_b200_postprocess_detections) keep one stream and grow-only device buffers PER CALLING THREAD (the reference's CPU
+ * functions are re-entrant; thread-local scratch keeps that without a lock).  They are freed when the thread exits;
+ * this frees them now. */
+void tk_b200_thread_release(void);
 
 /* Pinned (page-locked, portable) host memory for the host-buffer entry points. */
 TK_NODISCARD tk_error_code_t tk_b200_host_alloc(void** out_ptr, size_t size_bytes);

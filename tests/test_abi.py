@@ -65,6 +65,7 @@ def test_headers_are_plain_c_and_layouts_match(tmp_path):
         "tk_b200_pipeline_config_t": capi.PipelineConfig,
         "tk_object_detector_config_t": capi.ObjectDetectorConfig,
         "tk_b200_depth_metric_params_t": capi.DepthMetricParams, "tk_b200_distance_params_t": capi.DistanceParams,
+        "tk_b200_post_params_t": capi.PostParams,
     }
     body = "\n".join(f'    printf("{n} %zu\\n", sizeof({n}));' for n in structs)
     prog.write_text('#include <stdio.h>\n#include "tk_b200_vision.h"\nint main(void) {\n' + body +
@@ -93,6 +94,36 @@ def test_argument_validation_needs_no_gpu():
     assert lib.tk_preprocessor_resize_and_normalize_to_chw(None, None, 0, 0, None, None) == capi.TK_ERROR_INVALID_ARGUMENT
     assert lib.tk_error_to_string(capi.TK_ERROR_INVALID_DIMENSIONS) == b"invalid dimensions"
     assert lib.tk_b200_color_name(0) == b"red" and lib.tk_b200_color_name(8) == b"gray"
+
+
+def test_shard_block_and_gather_are_host_only():
+    """tk_b200_shard_block tiles [0, n) with blocks that differ by at most one frame; tk_b200_shard_gather is the final
+    host gather (prefix sum of the counts + memcpy) — neither needs a device."""
+    import numpy as np
+    lib = capi.lib()
+    for n in (0, 1, 7, 64, 1000, 1023):
+        for G in (1, 2, 3, 8):
+            lo, cnt = C.c_uint32(), C.c_uint32()
+            nxt, sizes = 0, []
+            for g in range(G):
+                lib.tk_b200_shard_block(C.c_uint32(n), C.c_uint32(g), C.c_uint32(G), C.byref(lo), C.byref(cnt))
+                assert lo.value == nxt
+                nxt += cnt.value; sizes.append(cnt.value)
+            assert nxt == n and max(sizes) - min(sizes) <= 1
+    rng = np.random.default_rng(0)
+    n, md = 9, 5
+    dets = rng.integers(0, 1 << 30, (n, md, 7), dtype=np.int32)
+    counts = np.array([0, 5, 3, 9, 1, 0, 5, 2, 4], np.uint32)          # 9 > md: clipped to md
+    offs = np.zeros(n + 1, np.uint64)
+    assert lib.tk_b200_shard_gather(None, counts.ctypes.data_as(C.c_void_p), n, md, None, offs.ctypes.data_as(C.c_void_p)) == 0
+    k = np.minimum(counts, md)
+    assert np.array_equal(offs, np.concatenate([[0], np.cumsum(k)]).astype(np.uint64))
+    flat = np.zeros((int(offs[-1]), 7), np.int32)
+    assert lib.tk_b200_shard_gather(dets.ctypes.data_as(C.c_void_p), counts.ctypes.data_as(C.c_void_p), n, md,
+                                    flat.ctypes.data_as(C.c_void_p), offs.ctypes.data_as(C.c_void_p)) == 0
+    for f in range(n):
+        assert np.array_equal(flat[int(offs[f]):int(offs[f + 1])], dets[f, :k[f]])
+    assert lib.tk_b200_shard_create(None, None, 0, None) == capi.TK_ERROR_INVALID_ARGUMENT
 
 
 def test_no_cpu_fallback_without_device():

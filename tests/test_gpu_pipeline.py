@@ -175,6 +175,17 @@ def test_stage_timing_and_launch_count():
         assert lib.tk_b200_launch_count() - before == 15      # pre + decode + nms per call
         ms, calls = pipe.stage_times()
         assert calls == 5 and all(m > 0 for m in ms)
+    for mode in (2, 3):                                       # the fused post-process forms: two launches per call
+        with make_pipe(n, fuse_postprocess=mode) as pipe:
+            t, d, c = pipe.alloc_outputs(n)
+            pipe.stage_timing(5)
+            before = lib.tk_b200_launch_count()
+            for _ in range(5):
+                pipe.process_device(df, dl, t, d, c)
+            torch.cuda.synchronize()
+            assert lib.tk_b200_launch_count() - before == 10
+            ms, calls = pipe.stage_times()
+            assert calls == 5 and ms[0] > 0 and ms[1] > 0 and ms[2] == 0
 
 
 def test_errors():
@@ -202,3 +213,63 @@ def test_postprocess_detections_reference_result_type():
         assert box == (r["x"], r["y"], r["w"], r["h"])
     # nothing above the threshold -> empty, NULL results
     assert V.postprocess_detections(logit, conf_thr=2.0) == []
+
+
+def test_shard_harness_one_process_several_pipelines():
+    """tk_b200_shard_*: one process, one host thread + one pipeline per entry of device_ids, contiguous frame blocks,
+    outputs written straight into the job's host arrays.  On a single-GPU box the ids repeat device 0 (three pipelines,
+    three host threads, one device); with more GPUs every device takes a block.  Against one pipeline over the whole
+    batch and against the oracle, twice per handle, with a threshold update in between."""
+    n_dev = max(torch.cuda.device_count(), 1)
+    ids = list(range(n_dev)) if n_dev > 1 else [0, 0, 0]
+    n = 11                                                   # not a multiple of the device count: ragged blocks
+    frames, logits = inputs(n, seed0=300)
+    kw = dict(max_batch=n, chunk_frames=2, width=W, height=H, tensor_w=64, tensor_h=48, out_dtype=torch.float32,
+              arith=V.ARITH_EXACT, num_proposals=P, num_classes=NC, conf_thr=0.5, iou_thr=0.5, max_detections=500)
+    hf, hl = torch.from_numpy(frames).pin_memory(), torch.from_numpy(logits).pin_memory()
+    with V.Shard(ids, **kw) as sh:
+        hd = torch.zeros((n, 500, 7), dtype=torch.int32).pin_memory()
+        hc = torch.zeros((n,), dtype=torch.int32).pin_memory()
+        ht = torch.zeros((n, 3, 48, 64), dtype=torch.float32).pin_memory()
+        for rep in range(2):
+            hd.zero_(); hc.zero_(); ht.zero_()
+            sh.process_host(hf, hl, hd, hc, tensor=ht)
+            check_dets(hd, hc, logits)
+            for i in range(n):
+                assert np.array_equal(ht[i].numpy().view(np.uint32), O.preprocess_rgb8(frames[i], 64, 48).view(np.uint32))
+        flat, offs = sh.gather(hd, hc)
+        assert int(offs[-1]) == int(hc.sum()) and len(offs) == n + 1
+        for f in range(n):
+            assert np.array_equal(flat[int(offs[f]):int(offs[f + 1])], hd[f, :int(hc[f])].numpy())
+        sh.update_thresholds(0.9, 0.5)                       # fewer rows pass on every device
+        sh.process_host(None, hl, hd, hc)
+        for i in range(n):
+            c, _ = O.decode(logits[i], 0.9, cap=4096)
+            ref = O.nms_classwise(c, 0.5, 500).view(V.CAND_DTYPE)
+            assert hd[i, :int(hc[i])].numpy().tobytes() == ref.tobytes()
+
+
+def test_shard_harness_from_c(tmp_path):
+    """tests/c/tk_shard_test.c: ONE C process drives every visible device (three pipelines on device 0 when there is
+    one) through tk_b200_shard_process_host and compares tensors, counts, detections and the gathered flat list with a
+    single tk_b200_pipeline over the whole batch, byte for byte; the detection total is checked against the oracle."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(__file__), "c", "tk_shard_test")
+    if not os.path.exists(exe):
+        pytest.fail("tests/c/tk_shard_test is not built: run __graft_entry__.build()")
+    n = 13
+    frames, logits = inputs(n, seed0=500)
+    fp, lp = tmp_path / "frames.u8", tmp_path / "logits.f32"
+    frames.tofile(fp)
+    logits.tofile(lp)
+    out = subprocess.run([exe, str(fp), str(lp), str(n), str(W), str(H), str(P), str(NC)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    words = out.stdout.split()
+    total = int(words[words.index("detections") + 1])
+    want = 0
+    for i in range(n):
+        c, _ = O.decode(logits[i], 0.5, cap=4096)
+        want += len(O.nms_classwise(c, 0.5, 300))
+    assert total == want > 0
+    print(out.stdout.strip())

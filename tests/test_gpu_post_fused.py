@@ -12,12 +12,22 @@ from trackiellm_b200 import vision as V
 pytestmark = pytest.mark.gpu
 
 
+LAYOUT = 0     # set per test by the `layout` fixture: 0 = a cluster of 8 CTAs per frame, 1 = persistent co-resident CTAs
+
+
+@pytest.fixture(autouse=True, params=[0, 1], ids=["cluster", "persistent"])
+def layout(request):
+    global LAYOUT
+    LAYOUT = request.param
+    yield request.param
+
+
 def fused(ts, thr, iou, max_det, act=V.ACT_RAW, cap=4096, agnostic=False, restore=None):
     d = torch.from_numpy(np.ascontiguousarray(ts)).cuda()
     if d.dim() == 2:
         d = d[None]
     c, n, dets, nd = V.postprocess_fused(d, thr, iou, max_det, act=act, max_candidates=cap, class_agnostic=agnostic,
-                                         restore=restore)
+                                         restore=restore, layout=LAYOUT)
     torch.cuda.synchronize()
     return V.candidates_to_numpy(c, n), n.cpu().numpy(), V.candidates_to_numpy(dets, nd)
 
@@ -97,7 +107,7 @@ def test_fused_equals_two_kernel_path_on_a_long_batch():
     ts = np.stack([synth.logits_tensor(500 + i, num_proposals=P, objects=int(rng.integers(0, 60)), dups=int(rng.integers(1, 16)),
                                        adversarial=(i % 50 == 0)) for i in range(n)])
     d = torch.from_numpy(ts).cuda()
-    c1, n1, d1, m1 = V.postprocess_fused(d, 0.5, 0.5, 300, max_candidates=1024)
+    c1, n1, d1, m1 = V.postprocess_fused(d, 0.5, 0.5, 300, max_candidates=1024, layout=LAYOUT)
     c2, n2 = V.decode_detections(d, 0.5, max_candidates=1024)
     d2, m2 = V.nms_classwise(c2, n2, 0.5, 300)
     torch.cuda.synchronize()
@@ -134,13 +144,14 @@ def test_fused_random_configs_bitexact():
 
 @pytest.mark.parametrize("n", [3, 40])
 def test_pipeline_fused_equals_separate(n):
-    """process_device with the post-process forked onto the side stream (fuse_postprocess = 2) against the three
-    kernels in a row (= 1): tensors, detections and counts identical; repeated calls on one stream stay ordered."""
+    """process_device with the cluster-fused post-process (fuse_postprocess = 3) and with the persistent form forked
+    onto the side stream (= 2) against the three kernels in a row (= 1, the default): tensors, detections and counts
+    identical; repeated calls on one stream stay ordered."""
     W, H, P = 320, 240, 4000
     frames = np.stack([synth.rgb_frame(W, H, 70 + i) for i in range(n)])
     logits = np.stack([synth.logits_tensor(70 + i, num_proposals=P, objects=20, dups=7, adversarial=(i == 0)) for i in range(n)])
     outs = []
-    for mode in (1, 2):
+    for mode in (1, 2, 3) if LAYOUT == 0 else (1, 2):
         with V.Pipeline(max_batch=n, width=W, height=H, tensor_w=96, tensor_h=64, out_dtype=torch.float32, arith=V.ARITH_EXACT,
                         num_proposals=P, num_classes=80, conf_thr=0.5, iou_thr=0.5, max_detections=300,
                         fuse_postprocess=mode) as pipe:
@@ -153,9 +164,43 @@ def test_pipeline_fused_equals_separate(n):
                     pipe.process_device(df, dl, dt, dd, dc)
             torch.cuda.synchronize()
             outs.append((dt.cpu().numpy().copy(), V.candidates_to_numpy(dd, dc), dc.cpu().numpy().copy()))
-    assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
-    assert np.array_equal(outs[0][2], outs[1][2])
+    for other in outs[1:]:
+        assert np.array_equal(outs[0][0].view(np.uint32), other[0].view(np.uint32))
+        assert np.array_equal(outs[0][2], other[2])
+        for f in range(n):
+            assert outs[0][1][f].tobytes() == other[1][f].tobytes()
     for f in range(n):
-        assert outs[0][1][f].tobytes() == outs[1][1][f].tobytes()
         rc, _ = O.decode(logits[f], 0.5, cap=4096)
         assert outs[1][1][f].tobytes() == O.nms_classwise(rc, 0.5, 300).tobytes()
+
+
+def test_no_candidate_is_dropped_silently():
+    """with a threshold low enough that more than 4096 rows pass, the capped kernels used to keep the first
+    4096 by index and say nothing.  Now (a) the separate launchers take any cap (NMS above 4096 candidates sorts in a
+    global work area), (b) the reference-typed entry point tk_b200_postprocess_detections, which has no cap in its
+    signature, answers what the UNTRUNCATED oracle answers (the reference keeps every candidate,
+    src/vision/tk_object_detector.c:339-355), (c) the pipeline reports the overflow."""
+    if LAYOUT == 1:
+        pytest.skip("layout-independent")
+    t = synth.logits_tensor(21, objects=200, dups=30)
+    thr = 0.2                                   # rows with U(0, 0.3) objectness pass too
+    rc, total = O.decode(t, thr)                # no cap
+    assert total > 8000
+    want = O.nms_classwise(rc, 0.5, 500)
+    d = torch.from_numpy(t[None]).cuda()
+    c, n = V.decode_detections(d, thr, max_candidates=25200)
+    dets, nd = V.nms_classwise(c, n, 0.5, 500)
+    torch.cuda.synchronize()
+    assert int(n[0]) == total
+    assert V.candidates_to_numpy(dets, nd)[0].tobytes() == want.tobytes()
+    _, _, got = fused(t, thr, 0.5, 500, cap=25200)
+    assert got[0].tobytes() == want.tobytes()
+    recs = V.postprocess_detections(t, conf_thr=thr, iou_thr=0.5, max_detections=500)
+    assert [(r[0], int(np.float32(r[2]).view(np.uint32)), r[3]) for r in recs] == \
+        [(int(k["class_id"]), int(np.float32(k["confidence"]).view(np.uint32)), (int(k["x"]), int(k["y"]), int(k["w"]), int(k["h"]))) for k in want]
+    with V.Pipeline(max_batch=1, width=64, height=48, tensor_w=32, tensor_h=32, out_dtype=torch.float32, conf_thr=thr,
+                    max_detections=500) as pipe:
+        _, hd, hc = pipe.alloc_outputs(1, pinned=True)
+        pipe.process_host(None, torch.from_numpy(t[None]).pin_memory(), hd, hc)
+        frames_over, max_count = pipe.candidate_overflow()
+        assert frames_over == 1 and max_count == total

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libtk_b200.so")
+# TK_B200_LIB: another build of the same library (the CHECKED build, tools/run_checked.sh); no other file is ever tried.
+LIB_PATH = os.environ.get("TK_B200_LIB") or os.path.join(PKG_DIR, "libtk_b200.so")
 
 TK_SUCCESS = 0
 TK_ERROR_INVALID_ARGUMENT = 1001
@@ -107,7 +108,7 @@ class PostParams(C.Structure):             # tk_b200_post_params_t
                 ("d_detections", C.c_void_p), ("d_num_detections", C.c_void_p),
                 ("restore_src_width", C.c_uint32), ("restore_src_height", C.c_uint32),
                 ("restore_in_width", C.c_uint32), ("restore_in_height", C.c_uint32),
-                ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t)]
+                ("d_workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("layout", C.c_int)]
 
 
 class ArgmaxParams(C.Structure):           # tk_b200_argmax_params_t

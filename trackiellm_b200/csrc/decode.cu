@@ -24,16 +24,28 @@
 //   * Sigmoid / softmax use tk_dm_expf (include/tk_b200_detmath.h), the same
 //     source the oracle compiles, so thresholds and scores agree bit for bit.
 #include "decode_row.cuh"
+#include "nms_frame.cuh"
 
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
 namespace tkb {
 
+// NMS tail of the fused form (tk_kernels_postprocess_fused, layout 0): once the eight CTAs of a frame's cluster have
+// written the candidate list, the first of them runs the class-wise NMS of that frame at once — in the shared memory
+// the decode phase no longer needs when the frame has <= 512 candidates, else through the frame's global scratch —
+// while the clusters of other frames are still decoding.  One launch instead of two, no gap between them, and the
+// NMS of the early frames hides under the decode tail of the late ones.
+struct NmsTail {
+    NmsK n;
+    uint8_t* scratch;        // [frames][nms_smem_bytes(scratch_pitch)], frames above kNmsSmall candidates
+    uint32_t scratch_pitch;
+};
+
 // 4 CTAs per SM (<= 32 registers): with 3, only 48 of the 64 clusters of the bench batch are
 // co-resident (a cluster of 8 must sit in one GPC) and the launch needs two waves.
-template <int ACT, bool PACKED>
-__global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
+template <int ACT, bool PACKED, bool NMS>
+__global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, const NmsTail tail) {
     extern __shared__ __align__(16) uint8_t dsm[];
     uint32_t* flags = reinterpret_cast<uint32_t*>(dsm);            // [nwords] ballot bitmap
     uint32_t* wpre = flags + k.nwords;                             // [nwords] exclusive prefix of popc
@@ -150,6 +162,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
     tk_b200_candidate_t* out = k.cands + (size_t)frame * k.cap;
     if (frame_pre < k.cap) {
         const uint32_t nrec = min(min(local_tot, kDecStage), k.cap - frame_pre);
+        TK_DEV_ASSERT(frame_pre + nrec <= k.cap && nrec <= kDecStage);
         uint32_t* dst = reinterpret_cast<uint32_t*>(out + frame_pre);
         for (uint32_t i = tid; i < nrec * 7; i += kDecThreads) dst[i] = stage[i];
     }
@@ -173,11 +186,23 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k) {
             }
         }
     }
+    if constexpr (NMS) {
+        // Every CTA of the cluster has written its slice of the frame's list (rank 0 also the count): release them to
+        // the first CTA, which goes on to the NMS; the others are done.
+        __syncthreads();
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        if (rank != 0) return;
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (min(frame_tot, k.cap) <= kNmsSmall) nms_frame<kDecThreads>(tail.n, frame, dsm, kNmsSmall);
+        else nms_frame<kDecThreads>(tail.n, frame, tail.scratch + (size_t)frame * nms_smem_bytes(tail.scratch_pitch), tail.scratch_pitch);
+    }
 }
 
 template <int ACT>
-static tk_error_code_t launch_decode(const DecK& k, uint32_t frames, size_t smem, cudaStream_t stream) {
-    auto kern = k.obj ? decode_kernel<ACT, true> : decode_kernel<ACT, false>;
+static tk_error_code_t launch_decode(const DecK& k, const NmsTail* tail, uint32_t frames, size_t smem, cudaStream_t stream) {
+    auto kern = tail ? (k.obj ? decode_kernel<ACT, true, true> : decode_kernel<ACT, false, true>)
+                     : (k.obj ? decode_kernel<ACT, true, false> : decode_kernel<ACT, false, false>);
+    const NmsTail t = tail ? *tail : NmsTail{};
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     cudaLaunchConfig_t cfg{};
@@ -189,19 +214,12 @@ static tk_error_code_t launch_decode(const DecK& k, uint32_t frames, size_t smem
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = kDecCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    TK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, k), TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE);
-    return launch_status("decode_kernel");
+    TK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, k, t), TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE);
+    return launch_status(tail ? "decode_kernel+nms" : "decode_kernel");
 }
 
-}  // namespace tkb
-
-using namespace tkb;
-
-extern "C" tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_params_t* p, cudaStream_t stream) {
-    return tkb::decode_detections_packed(p, nullptr, stream);
-}
-
-tk_error_code_t tkb::decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream) {
+static tk_error_code_t decode_launch_common(const tk_b200_decode_params_t* p, const float* d_objectness, const NmsTail* tail,
+                                            cudaStream_t stream) {
     if (!p || !p->d_logits || !p->d_counts || (!p->d_candidates && p->max_candidates)) return TK_ERROR_INVALID_ARGUMENT;
     if (p->num_frames == 0) return TK_SUCCESS;
     if (p->num_proposals == 0) return TK_ERROR_INVALID_DIMENSIONS;      // dims check of tk_object_detector.c:325-336
@@ -217,13 +235,37 @@ tk_error_code_t tkb::decode_detections_packed(const tk_b200_decode_params_t* p, 
     k.cap = p->max_candidates;
     k.thr = p->confidence_threshold;
     size_t smem = (size_t)k.nwords * 8 + (p->activation == TK_B200_ACT_SOFTMAX ? (size_t)kDecWarps * k.C * 4 : 0);
-    if (smem > (size_t)dev->max_smem_optin - 1024) {
+    if (tail && smem < nms_smem_bytes(kNmsSmall)) smem = nms_smem_bytes(kNmsSmall);   // the NMS phase overlays the decode buffers
+    if (smem > (size_t)dev->max_smem_optin - 1024 - 8192) {
         tk_error_set_detail("decode: %u proposals x %u classes need %zu B of shared memory", k.P, k.C, smem);
         return TK_ERROR_NOT_IMPLEMENTED;
     }
     switch (p->activation) {
-        case TK_B200_ACT_RAW:     return launch_decode<TK_B200_ACT_RAW>(k, p->num_frames, smem, stream);
-        case TK_B200_ACT_SIGMOID: return launch_decode<TK_B200_ACT_SIGMOID>(k, p->num_frames, smem, stream);
-        default:                  return launch_decode<TK_B200_ACT_SOFTMAX>(k, p->num_frames, smem, stream);
+        case TK_B200_ACT_RAW:     return launch_decode<TK_B200_ACT_RAW>(k, tail, p->num_frames, smem, stream);
+        case TK_B200_ACT_SIGMOID: return launch_decode<TK_B200_ACT_SIGMOID>(k, tail, p->num_frames, smem, stream);
+        default:                  return launch_decode<TK_B200_ACT_SOFTMAX>(k, tail, p->num_frames, smem, stream);
     }
+}
+
+}  // namespace tkb
+
+using namespace tkb;
+
+extern "C" tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_params_t* p, cudaStream_t stream) {
+    return tkb::decode_detections_packed(p, nullptr, stream);
+}
+
+tk_error_code_t tkb::decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream) {
+    return decode_launch_common(p, d_objectness, nullptr, stream);
+}
+
+// tk_kernels_postprocess_fused, layout 0: decode_kernel with the NMS tail.  `n` comes filled from post.cu
+// (postprocess_fused_packed validates and builds it); scratch: [frames][nms_smem_bytes(pitch)] when the cap is above 512.
+tk_error_code_t tkb::decode_nms_cluster(const tk_b200_decode_params_t* p, const float* d_objectness, const void* nms_k,
+                                        void* scratch, uint32_t scratch_pitch, cudaStream_t stream) {
+    NmsTail t{};
+    t.n = *static_cast<const NmsK*>(nms_k);
+    t.scratch = static_cast<uint8_t*>(scratch);
+    t.scratch_pitch = scratch_pitch;
+    return decode_launch_common(p, d_objectness, &t, stream);
 }

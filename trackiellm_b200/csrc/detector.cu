@@ -180,7 +180,7 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
     if ((rc = reserve(d, 1, tensor_bytes)) != TK_SUCCESS) return rc;
     if ((rc = reserve(d, 2, logit_bytes)) != TK_SUCCESS) return rc;
     if ((rc = reserve(d, 3, off_cnt + 8 * (size_t)n + 256)) != TK_SUCCESS) return rc;
-    if ((rc = reserve_pinned(d, det_bytes + 4 * (size_t)n)) != TK_SUCCESS) return rc;
+    if ((rc = reserve_pinned(d, det_bytes + 8 * (size_t)n)) != TK_SUCCESS) return rc;
 
     uint8_t* d_frames = static_cast<uint8_t*>(d->d_buf[0]);
     float* d_tensor = static_cast<float*>(d->d_buf[1]);
@@ -224,12 +224,34 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
     np.restore_src_width = f0.width; np.restore_src_height = f0.height; np.restore_in_width = W; np.restore_in_height = H;   // :365
     if ((rc = tk_kernels_nms_classwise(&np, st)) != TK_SUCCESS) return rc;
 
-    uint32_t* h_cnt = reinterpret_cast<uint32_t*>(d->h_pinned + det_bytes);
+    uint32_t* h_cnt = reinterpret_cast<uint32_t*>(d->h_pinned + det_bytes);       // [n] detections, then [n] candidates
     tk_b200_candidate_t* h_det = reinterpret_cast<tk_b200_candidate_t*>(d->h_pinned);
     TK_CUDA_TRY(cudaMemcpyAsync(h_cnt, d_cnt + n, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    TK_CUDA_TRY(cudaMemcpyAsync(h_cnt + n, d_cnt, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
     TK_CUDA_TRY(cudaMemcpyAsync(h_det, d_d, det_bytes, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
     if (cudaStreamSynchronize(st) != cudaSuccess) {
         tk_error_set_detail("detect: %s", cudaGetErrorString(cudaGetLastError()));
+        return TK_ERROR_INFERENCE_FAILED;
+    }
+    // The reference keeps every row that passes the threshold (:339-355); the kernels above cap a frame at kDetCap
+    // candidates.  A frame that went over (a low threshold, a crowd) is done again without a cap — never truncated.
+    bool redone = false;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (h_cnt[n + i] <= kDetCap) continue;
+        const uint32_t restore[4] = {f0.width, f0.height, W, H};
+        if ((rc = postprocess_frame_uncapped(d_logits + (size_t)i * P * L, P, C, d->activation, d->config.confidence_threshold,
+                                             d->config.iou_threshold, kDetMax, 0, restore, d_d + (size_t)i * kDetMax,
+                                             d_cnt + n + i, st)) != TK_SUCCESS) {
+            cudaStreamSynchronize(st);
+            return rc;
+        }
+        TK_CUDA_TRY(cudaMemcpyAsync(h_cnt + i, d_cnt + n + i, 4, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+        TK_CUDA_TRY(cudaMemcpyAsync(h_det + (size_t)i * kDetMax, d_d + (size_t)i * kDetMax, kDetMax * sizeof(tk_b200_candidate_t),
+                                    cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+        redone = true;
+    }
+    if (redone && cudaStreamSynchronize(st) != cudaSuccess) {
+        tk_error_set_detail("detect (uncapped frame): %s", cudaGetErrorString(cudaGetLastError()));
         return TK_ERROR_INFERENCE_FAILED;
     }
 

@@ -24,6 +24,23 @@ struct HostScratch {
     cudaStream_t stream = nullptr;
     void* buf[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t cap[4] = {0, 0, 0, 0};
+    // Frees the thread's stream and device buffers (thread exit, or tk_b200_thread_release): a short-lived thread that
+    // calls a host entry point must not leave device memory behind.  At process teardown the runtime may already be
+    // gone; every call here tolerates that.
+    void release() {
+        if (device < 0) return;
+        int cur = -1;
+        const bool have_cur = cudaGetDevice(&cur) == cudaSuccess;
+        if (cudaSetDevice(device) == cudaSuccess) {
+            if (stream) cudaStreamSynchronize(stream);
+            for (int i = 0; i < 4; ++i) { if (buf[i]) cudaFree(buf[i]); buf[i] = nullptr; cap[i] = 0; }
+            if (stream) cudaStreamDestroy(stream);
+            if (have_cur && cur >= 0) cudaSetDevice(cur);
+        }
+        cudaGetLastError();
+        stream = nullptr; device = -1;
+    }
+    ~HostScratch() { release(); }
 };
 static thread_local HostScratch g_hs;
 
@@ -93,9 +110,10 @@ __global__ void __launch_bounds__(1024) boxes_to_candidates_kernel(const float* 
 }
 
 __global__ void candidates_to_indices_kernel(const tk_b200_candidate_t* __restrict__ dets, const uint32_t* __restrict__ n,
-                                             int32_t* __restrict__ indices, uint32_t max_det) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < max_det) indices[i] = i < *n ? dets[i].index : -1;
+                                             int32_t* __restrict__ indices, uint32_t md, uint32_t max_det) {
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < max_det;
+         i += (unsigned long long)gridDim.x * blockDim.x)
+        indices[i] = (i < md && i < *n) ? dets[i].index : -1;
 }
 
 }  // namespace tkb
@@ -121,7 +139,7 @@ extern "C" tk_error_code_t tk_cuda_tensor_nms(tk_cuda_dispatcher_t* dispatcher, 
     int prev = -1; cudaGetDevice(&prev);
     if (cudaSetDevice(dev) != cudaSuccess) { cudaGetLastError(); return TK_ERROR_GPU_DEVICE_SET_FAILED; }
     cudaStream_t st = tk_b200_dispatch_stream(dispatcher);
-    const uint32_t cap = K < 4096u ? K : 4096u;
+    const uint32_t cap = K;                                    // every box is a candidate (above 4096: the global NMS path)
     const uint32_t md = max_detections < cap ? max_detections : cap;
     tk_error_code_t rc = TK_SUCCESS;
     uint8_t* scratch = nullptr;
@@ -147,7 +165,10 @@ extern "C" tk_error_code_t tk_cuda_tensor_nms(tk_cuda_dispatcher_t* dispatcher, 
             rc = tk_kernels_nms_classwise(&np, st);
         }
         if (rc == TK_SUCCESS) {
-            candidates_to_indices_kernel<<<(max_detections + 255) / 256, 256, 0, st>>>(d_d, d_cnt + 1, static_cast<int32_t*>(indices->d_ptr), md);
+            // indices[0, n) = kept boxes, [n, max_detections) = -1 (the whole buffer the caller sized is defined)
+            uint32_t blocks = max_detections / 256 + (max_detections % 256 ? 1u : 0u);
+            if (blocks > 1024u) blocks = 1024u;                 // grid-stride loop inside
+            candidates_to_indices_kernel<<<blocks, 256, 0, st>>>(d_d, d_cnt + 1, static_cast<int32_t*>(indices->d_ptr), md, max_detections);
             rc = launch_status("candidates_to_indices_kernel");
         }
         if (rc == TK_SUCCESS && cudaMemcpyAsync(&host_n, d_cnt + 1, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = TK_ERROR_GPU_MEMORY_COPY_FAILED;
@@ -301,9 +322,19 @@ extern "C" tk_error_code_t tk_b200_postprocess_detections(
         m.restore_src_width = frame_w; m.restore_src_height = frame_h; m.restore_in_width = in_w; m.restore_in_height = in_h;
     }
     if ((rc = tk_kernels_nms_classwise(&m, s->stream)) != TK_SUCCESS) return rc;
-    uint32_t n = 0;
-    TK_CUDA_TRY(cudaMemcpyAsync(&n, d_n + 1, 4, cudaMemcpyDeviceToHost, s->stream), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    uint32_t cnt[2] = {0, 0};                                  // rows over the threshold, kept detections
+    TK_CUDA_TRY(cudaMemcpyAsync(cnt, d_n, 8, cudaMemcpyDeviceToHost, s->stream), TK_ERROR_GPU_MEMORY_COPY_FAILED);
     TK_CUDA_TRY(cudaStreamSynchronize(s->stream), TK_ERROR_CUDA_KERNEL_FAILURE);
+    if (cnt[0] > cap) {
+        // more candidates than the capped kernels hold: the reference keeps them all (:339-355) — again, uncapped
+        const uint32_t restore[4] = {frame_w, frame_h, in_w, in_h};
+        const bool any = frame_w && frame_h && in_w && in_h;
+        if ((rc = postprocess_frame_uncapped(static_cast<const float*>(s->buf[0]), P, C, act, conf_thr, iou_thr, max_det, 0,
+                                             any ? restore : nullptr, d_d, d_n + 1, s->stream)) != TK_SUCCESS) return rc;
+        TK_CUDA_TRY(cudaMemcpyAsync(cnt, d_n, 8, cudaMemcpyDeviceToHost, s->stream), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+        TK_CUDA_TRY(cudaStreamSynchronize(s->stream), TK_ERROR_CUDA_KERNEL_FAILURE);
+    }
+    const uint32_t n = cnt[1];
     if (n == 0) return TK_SUCCESS;
     tk_b200_candidate_t* tmp = static_cast<tk_b200_candidate_t*>(malloc((size_t)n * sizeof(tk_b200_candidate_t)));
     tk_detection_result_t* res = static_cast<tk_detection_result_t*>(calloc(n, sizeof(tk_detection_result_t)));
@@ -326,6 +357,10 @@ extern "C" tk_error_code_t tk_b200_postprocess_detections(
 extern "C" void tk_object_detector_free_results(tk_detection_result_t** results) {
     if (results && *results) { free(*results); *results = nullptr; }
 }
+
+// Drops the calling thread's scratch (stream + device buffers of the host-pointer entry points) now instead of at
+// thread exit.
+extern "C" void tk_b200_thread_release(void) { tkb::g_hs.release(); }
 
 // Pinned host memory so the batched host entry points copy by DMA.
 extern "C" tk_error_code_t tk_b200_host_alloc(void** out, size_t bytes) {

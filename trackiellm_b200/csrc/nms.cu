@@ -25,7 +25,11 @@
 //   * a class segment longer than 64 (a crowd of one class, class-agnostic mode)
 //     switches the frame to the blocked path: 64-column blocks of the suppression
 //     matrix over the score-sorted list (diagonal block per thread, one-thread
-//     resolve, CTA-wide sweep).
+//     resolve, CTA-wide sweep);
+//   * more than 4096 candidates per frame (the shared-memory limit): the same nms_frame code with its work area in a
+//     stream-ordered global scratch (nms_global_kernel) — slow, rare, and what keeps a low threshold or a crowded frame
+//     from being silently truncated: the reference keeps every candidate (calloc(num_proposals),
+//     src/vision/tk_object_detector.c:339-355).
 #include "nms_frame.cuh"
 
 namespace tkb {
@@ -42,6 +46,15 @@ __global__ void __launch_bounds__(kNmsThreads, 3) nms_kernel(const NmsK k) {
     }
 }
 
+// Any number of candidates per frame: the work area of each CTA lives in global memory (L2-resident while it is hot).
+__global__ void __launch_bounds__(kNmsThreads, 2) nms_global_kernel(const NmsK k, uint8_t* scratch, const uint32_t pitch) {
+    uint8_t* work = scratch + (size_t)blockIdx.x * nms_smem_bytes(pitch);
+    for (uint32_t frame = blockIdx.x; frame < k.num_frames; frame += gridDim.x) {
+        nms_frame<kNmsThreads>(k, frame, work, pitch);
+        __syncthreads();
+    }
+}
+
 }  // namespace tkb
 
 using namespace tkb;
@@ -51,11 +64,7 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
         (!p->d_detections && p->max_detections))
         return TK_ERROR_INVALID_ARGUMENT;
     if (p->num_frames == 0) return TK_SUCCESS;
-    if (p->max_candidates > kNmsMaxK) {
-        tk_error_set_detail("nms: max_candidates %u exceeds the %u candidates one CTA sorts in shared memory",
-                            p->max_candidates, kNmsMaxK);
-        return TK_ERROR_NOT_IMPLEMENTED;
-    }
+    if (p->max_candidates > (1u << 30)) return TK_ERROR_INVALID_ARGUMENT;
     const DeviceInfo* dev = device_info();
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
     NmsK k{};
@@ -72,6 +81,22 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
         k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
     }
     k.num_frames = p->num_frames;
+    if (p->max_candidates > kNmsMaxK) {
+        // above the shared-memory layout: global work areas from the stream-ordered allocator, one per CTA
+        uint32_t pitch = 2 * kNmsMaxK;
+        while (pitch < p->max_candidates) pitch <<= 1;
+        const uint32_t grid = p->num_frames < 2u * (uint32_t)dev->sm_count ? p->num_frames : 2u * (uint32_t)dev->sm_count;
+        uint8_t* scratch = nullptr;
+        if (cudaMallocAsync(reinterpret_cast<void**>(&scratch), (size_t)grid * nms_smem_bytes(pitch), stream) != cudaSuccess) {
+            tk_error_set_detail("nms: %zu B of scratch for %u candidates per frame: %s", (size_t)grid * nms_smem_bytes(pitch),
+                                p->max_candidates, cudaGetErrorString(cudaGetLastError()));
+            return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
+        }
+        nms_global_kernel<<<grid, kNmsThreads, 0, stream>>>(k, scratch, pitch);
+        const tk_error_code_t rc = launch_status("nms_global_kernel");
+        cudaFreeAsync(scratch, stream);
+        return rc;
+    }
     const size_t smem = nms_smem_bytes(k.Kp);
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);

@@ -6,7 +6,7 @@
 namespace tkb {
 
 static constexpr int kNmsThreads = 512;     // nms_kernel's CTA; the fused post-process kernel runs nms_frame with 256
-static constexpr uint32_t kNmsMaxK = 4096;
+static constexpr uint32_t kNmsMaxK = 4096;   // nms_kernel: the most candidates one CTA holds in shared memory (200 KB)
 
 struct NmsK {
     const tk_b200_candidate_t* cands;
@@ -38,8 +38,8 @@ __device__ __forceinline__ float iou_rect(int4 a, int4 b) {
     return uni > 0.0f ? __fdiv_rn(inter, uni) : 0.0f;
 }
 
-// Shared memory: keys u64, box int4, pos u32, cls u32, dead u8, keys2 u64, segmask u64 per entry.
-__host__ __device__ inline size_t nms_smem_bytes(uint32_t Kp) { return (size_t)Kp * (8 + 16 + 4 + 4 + 1 + 8 + 8); }
+// Work area: keys u64, box int4, pos u32, cls u32, dead u8, keys2 u64, segmask u64 per entry + one kept bit per entry.
+__host__ __device__ inline size_t nms_smem_bytes(uint32_t Kp) { return (size_t)Kp * (8 + 16 + 4 + 4 + 1 + 8 + 8) + Kp / 8; }
 
 // Bitonic sort of Kp 64-bit keys in shared memory (ascending), optional u32 payload.
 template <int THREADS, bool PAYLOAD>
@@ -102,7 +102,6 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     constexpr int kNmsWarps = THREADS / 32;
     __shared__ unsigned long long diag[64];
     __shared__ unsigned long long blk_kept;
-    __shared__ unsigned long long keptbits[kNmsMaxK / 64];
     __shared__ uint32_t warp_tot[kNmsWarps];
     __shared__ uint32_t seg_overflow;
 
@@ -114,6 +113,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     if ((k.select == 1 && K > kNmsSmall) || (k.select == 2 && K <= kNmsSmall)) return;    // the other launch's frame
     uint32_t Kp = 64;
     while (Kp < K) Kp <<= 1;                                       // sort only what this frame needs
+    TK_DEV_ASSERT(Kp <= pitch && (reinterpret_cast<uintptr_t>(dsm) & 15u) == 0);
 
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(dsm);          // [Kp] score keys
     int4* box = reinterpret_cast<int4*>(keys + pitch);                               // [Kp] score order
@@ -122,8 +122,9 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     uint8_t* dead = reinterpret_cast<uint8_t*>(cls + pitch);                         // [Kp] blocked path
     unsigned long long* keys2 = reinterpret_cast<unsigned long long*>(dead + pitch); // [Kp] (class << 32 | score rank)
     unsigned long long* segmask = keys2 + pitch;                                     // [Kp] class order
+    unsigned long long* keptbits = segmask + pitch;                                  // [Kp / 64] kept flags by score rank
 
-    if (tid < kNmsMaxK / 64) keptbits[tid] = 0ull;
+    for (uint32_t i = tid; i < (Kp >> 6); i += THREADS) keptbits[i] = 0ull;
     if (tid == 0) seg_overflow = 0;
     bool reg_sort = false;
     if constexpr (THREADS == 512) reg_sort = Kp <= 512;
@@ -254,6 +255,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
                 if (wpre[mid] <= pi) lo = mid; else hi = mid - 1;
             }
             uint32_t t = lo, w0 = wpre[t], R = wpre[t + 1] - w0, r = pi - w0;
+            TK_DEV_ASSERT(t < K && R <= t && r < R && (uint32_t)keys2[t] < K);
             int4 me = box[(uint32_t)keys2[t]];
             unsigned long long m = 0;
             for (; pi < pend; ++pi) {

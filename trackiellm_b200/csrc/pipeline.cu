@@ -10,14 +10,16 @@
 // ordered by events (the reference's dispatcher creates three streams and never
 // orders them, src/gpu/cuda/tk_cuda_dispatch.cu:107-137).
 //
-// Nothing here computes on the CPU.
+// The host side moves bytes (chunked copies, packing the objectness column of page-locked logits into a dense array);
+// it computes nothing: thresholds, boxes, scores and suppression are all decided on the device.
 #include "tk_common.cuh"
 
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include <new>
-#include <thread>
-#include <vector>
+
+#include "host_pool.h"
 
 namespace tkb {
 
@@ -42,7 +44,7 @@ struct tk_b200_pipeline_s {
     cudaStream_t s_up, s_compute, s_down, s_post;
     cudaStream_t s_side;                               // process_device: the fused post-process kernel runs here, under the pre-process kernel
     cudaEvent_t ev_post, ev_fork, ev_join;
-    int fused;                                         // decode + NMS as ONE co-resident kernel (post.cu)
+    int fused;                                         // fuse_postprocess: 0 / 1 separate kernels (default), 2 co-resident, 3 cluster-fused
     void* d_post_ws; size_t post_ws_bytes;             // its global NMS work area (frames above 512 candidates)
     cudaEvent_t ev_uploaded[tkb::kSlots], ev_computed[tkb::kSlots], ev_downloaded[tkb::kSlots];
     uint8_t* d_frames[tkb::kSlots];                    // [chunk][frame_bytes (+ slack)]
@@ -54,6 +56,11 @@ struct tk_b200_pipeline_s {
     uint32_t* d_ndets;                                 // [max_batch]
     float* h_obj;                                      // [max_batch][P] page-locked: objectness column packed on the host
     float* d_obj;                                      // [max_batch][P]
+    tkb::HostPool* pool;                               // host threads that pack it (created on first use, NUMA-local to the GPU)
+    uint32_t* h_cand_counts;                           // [max_batch] page-locked: rows over the threshold per frame of the last host call
+    uint32_t counts_valid, over_frames, over_max;      // ... and what they say about the candidate cap
+    std::mutex thr_mu;                                 // guards thr_conf / thr_iou (update_thresholds vs a running call)
+    float thr_conf, thr_iou;
     // Optional per-stage timing of process_device: 4 events per call (before pre,
     // after pre, after decode, after nms) on the caller's stream.
     int timing_on;
@@ -97,6 +104,8 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->d_ndets) cudaFree(p->d_ndets);
         if (p->d_obj) cudaFree(p->d_obj);
         if (p->h_obj) cudaFreeHost(p->h_obj);
+        if (p->h_cand_counts) cudaFreeHost(p->h_cand_counts);
+        delete p->pool;
         for (uint32_t i = 0; p->timing_ev && i < p->timing_cap * 4; ++i) if (p->timing_ev[i]) cudaEventDestroy(p->timing_ev[i]);
         free(p->timing_ev); free(p->timing_mode);
         if (p->s_up) cudaStreamDestroy(p->s_up);
@@ -134,6 +143,7 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     tk_b200_pipeline_t* p = new (std::nothrow) tk_b200_pipeline_t();
     if (!p) return TK_ERROR_OUT_OF_MEMORY;
     p->cfg = *cfg;
+    p->thr_conf = cfg->confidence_threshold; p->thr_iou = cfg->iou_threshold;
     if (p->cfg.max_candidates == 0) p->cfg.max_candidates = 4096;
     if (p->cfg.max_detections == 0) p->cfg.max_detections = 500;      // TK_OBJECT_DETECTOR_MAX_DETECTIONS, tk_object_detector.c:39
     p->chunk = cfg->chunk_frames ? cfg->chunk_frames : 8;
@@ -173,12 +183,12 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_counts), mb * sizeof(uint32_t)) == cudaSuccess;
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_dets), mb * p->cfg.max_detections * sizeof(tk_b200_candidate_t)) == cudaSuccess;
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_ndets), mb * sizeof(uint32_t)) == cudaSuccess;
-    // decode + NMS fused into one co-resident kernel: fuse_postprocess 0 = automatic (on for batches that give every
-    // persistent CTA at least ... see run_kernels), 1 = never, 2 = always; TK_B200_POST_FUSED overrides (experiments).
+    ok = ok && cudaHostAlloc(reinterpret_cast<void**>(&p->h_cand_counts), mb * sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess;
+    // decode + NMS as one kernel (post_mode); TK_B200_POST_FUSED overrides fuse_postprocess (experiments).
     p->fused = cfg->fuse_postprocess;
     if (const char* e = getenv("TK_B200_POST_FUSED")) p->fused = atoi(e);
-    if (ok && p->fused != 1) {
-        p->post_ws_bytes = tk_b200_postprocess_fused_workspace_bytes(p->cfg.max_candidates);
+    if (ok && (p->fused == 2 || p->fused == 3)) {
+        p->post_ws_bytes = tk_b200_postprocess_fused_workspace_bytes(p->cfg.max_candidates, cfg->max_batch, p->fused == 2 ? 1 : 0);
         if (p->post_ws_bytes) ok = cudaMalloc(&p->d_post_ws, p->post_ws_bytes) == cudaSuccess;
     }
     if (!ok) {
@@ -190,11 +200,62 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     return TK_SUCCESS;
 }
 
-// src/vision/tk_object_detector.c:212-219
+// src/vision/tk_object_detector.c:212-219; the reference's pipeline calls it under its mutex
+// (src/vision/tk_vision_pipeline.c:131-150).  Safe against a process_* call running on another thread: the new values
+// are picked up by the next call.
 extern "C" tk_error_code_t tk_b200_pipeline_update_thresholds(tk_b200_pipeline_t* p, float conf, float iou) {
     if (!p) return TK_ERROR_INVALID_ARGUMENT;
-    p->cfg.confidence_threshold = conf;
-    p->cfg.iou_threshold = iou;
+    std::lock_guard<std::mutex> lk(p->thr_mu);
+    p->thr_conf = conf;
+    p->thr_iou = iou;
+    return TK_SUCCESS;
+}
+
+// After tk_b200_pipeline_process_host[_frames]: frames of that call whose rows over the confidence threshold
+// outnumbered max_candidates (their candidate lists were cut to the first max_candidates rows by proposal index
+// before NMS — the reference keeps every candidate, src/vision/tk_object_detector.c:339-355), and the largest count.
+extern "C" tk_error_code_t tk_b200_pipeline_candidate_overflow(tk_b200_pipeline_t* p, uint32_t* out_frames, uint32_t* out_max_count) {
+    if (!p) return TK_ERROR_INVALID_ARGUMENT;
+    if (out_frames) *out_frames = p->over_frames;
+    if (out_max_count) *out_max_count = p->over_max;
+    return TK_SUCCESS;
+}
+// process_device leaves the per-frame counts of rows over the threshold on the device: [n] u32, valid once the call's
+// work on the stream has completed.
+extern "C" const uint32_t* tk_b200_pipeline_candidate_counts_device_ptr(tk_b200_pipeline_t* p) { return p ? p->d_counts : nullptr; }
+
+// Host threads + page-locked column for the objectness packing of process_host, created on first use.  The workers
+// are bound to the CPUs of the GPU's NUMA node when sysfs names them, and the column is allocated (first touched) by
+// one of them, so the packed bytes sit on the memory next to the link they cross.
+static tk_error_code_t ensure_pack_resources(tk_b200_pipeline_t* p) {
+    if (!p->pool) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        unsigned T = hw >= 16 ? 4u : (hw >= 4 ? 2u : 1u);
+        if (const char* e = getenv("TK_B200_PACK_THREADS")) { const int v = atoi(e); if (v >= 1 && v <= 64) T = (unsigned)v; }
+        cpu_set_t cpus;
+        char bdf[32] = {0};
+        const bool local = cudaDeviceGetPCIBusId(bdf, (int)sizeof(bdf), p->cfg.device_id) == cudaSuccess && tkb::pci_local_cpus(bdf, &cpus);
+        if (!local) cudaGetLastError();
+        p->pool = new (std::nothrow) tkb::HostPool(T - 1, local ? &cpus : nullptr);
+        if (!p->pool) return TK_ERROR_OUT_OF_MEMORY;
+    }
+    if (!p->h_obj || !p->d_obj) {
+        const size_t ob = (size_t)p->cfg.max_batch * p->cfg.num_proposals * sizeof(float);
+        cudaError_t e_host = cudaSuccess;
+        if (!p->h_obj) {
+            const int dev = p->cfg.device_id;
+            float** slot = &p->h_obj;
+            p->pool->parallel_for([&](unsigned part, unsigned parts) {       // allocate from the last (bound) worker
+                if (part != parts - 1) return;
+                cudaSetDevice(dev);
+                e_host = cudaHostAlloc(reinterpret_cast<void**>(slot), ob, cudaHostAllocDefault);
+            });
+        }
+        if (e_host != cudaSuccess || (!p->d_obj && cudaMalloc(reinterpret_cast<void**>(&p->d_obj), ob) != cudaSuccess)) {
+            tk_error_set_detail("pipeline objectness staging: %s", cudaGetErrorString(cudaGetLastError()));
+            return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
+        }
+    }
     return TK_SUCCESS;
 }
 
@@ -214,37 +275,35 @@ static tk_b200_preprocess_batch_params_t pre_params(const tk_b200_pipeline_t* p,
     return b;
 }
 
-// Whether `n` frames take the fused co-resident post-process kernel: one persistent 256-thread CTA works a whole frame
-// (~70 us of latency-bound work), which pays when there are frames enough to spread over the SMs and a pre-process
-// kernel long enough to hide it under; a handful of frames is faster through the 8-CTA-per-frame decode_kernel.
-static bool use_fused(const tk_b200_pipeline_t* p, uint32_t n) {
+// How `n` frames are post-processed: 0 decode_kernel then nms_kernel (the default: fastest as measured);
+// 3 ONE kernel, a cluster of 8 CTAs per frame that decodes and then runs the frame's NMS
+// (tk_kernels_postprocess_fused layout 0); 2 the persistent co-resident form (layout 1) forked onto the side stream
+// beside the pre-process kernel.  Both fused forms are bit-identical to the default and selectable, never automatic.
+static int post_mode(const tk_b200_pipeline_t* p, uint32_t n) {
     (void)n;
-    return p->fused == 2;        // automatic stays off until the co-resident step beats the three kernels in a row
+    return (p->fused == 2 || p->fused == 3) ? p->fused : 0;
 }
 
-// The launches for `n` frames whose inputs are in HBM: the pre-process kernel on `st`, and
-//   separate : decode_kernel, nms_kernel behind it on `st` (3 launches);
-//   fused    : post_kernel (decode + NMS per frame) on the side stream, forked off `st` before the pre-process launch
-//              and joined after it (2 launches): the two kernels share no data and are sized to be resident together
-//              (post.cu), so the post-process runs UNDER the pre-process kernel.
-// tev (stage timing): [0] start, [1] pre-process done, [2] decode done (fused: post_kernel done, recorded on the side
-// stream), [3] end.
+// The launches for `n` frames whose inputs are in HBM: the pre-process kernel on `st`, then the post-process on `st`
+// (mode 3: one launch; mode 0: two), or — mode 2 — post_kernel on the side stream, forked off `st` before the
+// pre-process launch and joined after it.
+// tev (stage timing): [0] start, [1] pre-process done, [2] decode done (fused: the whole post-process done; mode 2:
+// recorded on the side stream), [3] end.  *out_mode: 0 separate kernels, 1 fused in-stream, 2 fused beside.
 static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits, uint32_t n,
                                    void* d_tensor, tk_b200_candidate_t* d_cands, uint32_t* d_counts,
                                    tk_b200_candidate_t* d_dets, uint32_t* d_ndets, cudaStream_t st,
-                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr, uint8_t* out_fused = nullptr) {
+                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr, uint8_t* out_mode = nullptr) {
     const tk_b200_pipeline_config_t& c = p->cfg;
     tk_error_code_t rc;
-    if (out_fused) *out_fused = 0;
+    if (out_mode) *out_mode = 0;
     if (d_logits && (!d_dets || !d_ndets)) return TK_ERROR_INVALID_ARGUMENT;
     if (d_frames && !d_tensor) return TK_ERROR_INVALID_ARGUMENT;
     if (d_logits && c.restore_coordinates && c.resize_mode != TK_B200_RESIZE_STRETCH)
         return TK_ERROR_NOT_IMPLEMENTED;   // a letterboxed tensor would also need the pad offsets, which the reference
                                            // never defines (convert_to_original_coordinates is empty)
-    const bool fused = d_logits && use_fused(p, n);
-    bool fork = fused && d_frames;                             // something to run beside
-    if (tev) cudaEventRecord(tev[0], st);
-    if (fused) {
+    int mode = d_logits ? post_mode(p, n) : 0;
+    const bool fork = mode == 2 && d_frames;                   // something to run beside
+    auto fused_params = [&](int layout) {
         tk_b200_post_params_t q{};
         q.d_logits = d_logits; q.num_frames = n; q.num_proposals = c.num_proposals; q.num_classes = c.num_classes;
         q.confidence_threshold = c.confidence_threshold; q.activation = c.activation;
@@ -255,25 +314,25 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
             q.restore_src_width = c.input_width; q.restore_src_height = c.input_height;
             q.restore_in_width = c.tensor_width; q.restore_in_height = c.tensor_height;
         }
-        q.d_workspace = p->d_post_ws; q.workspace_bytes = p->post_ws_bytes;
-        cudaStream_t ps = fork ? p->s_side : st;
-        if (fork) {
-            TK_CUDA_TRY(cudaEventRecord(p->ev_fork, st), TK_ERROR_GPU_CUDA_ERROR);
-            TK_CUDA_TRY(cudaStreamWaitEvent(ps, p->ev_fork, 0), TK_ERROR_GPU_CUDA_ERROR);
-        }
-        rc = postprocess_fused_packed(&q, d_obj, ps);
-        if (rc == TK_ERROR_NOT_IMPLEMENTED) {
-            fork = false;                                      // head shapes the fused kernel's 25 KB do not hold: the two-kernel path below
+        q.d_workspace = p->d_post_ws; q.workspace_bytes = p->post_ws_bytes; q.layout = layout;
+        return q;
+    };
+    if (tev) cudaEventRecord(tev[0], st);
+    bool post_done = false;
+    if (fork) {
+        TK_CUDA_TRY(cudaEventRecord(p->ev_fork, st), TK_ERROR_GPU_CUDA_ERROR);
+        TK_CUDA_TRY(cudaStreamWaitEvent(p->s_side, p->ev_fork, 0), TK_ERROR_GPU_CUDA_ERROR);
+        const tk_b200_post_params_t q = fused_params(1);
+        rc = postprocess_fused_packed(&q, d_obj, p->s_side);
+        if (rc == TK_SUCCESS) {
+            if (tev) cudaEventRecord(tev[2], p->s_side);
+            TK_CUDA_TRY(cudaEventRecord(p->ev_join, p->s_side), TK_ERROR_GPU_CUDA_ERROR);
+            post_done = true;
+            if (out_mode) *out_mode = 2;
+        } else if (rc != TK_ERROR_NOT_IMPLEMENTED) {
+            return rc;
         } else {
-            if (rc != TK_SUCCESS) return rc;
-            if (fork) {
-                if (tev) cudaEventRecord(tev[2], ps);
-                TK_CUDA_TRY(cudaEventRecord(p->ev_join, ps), TK_ERROR_GPU_CUDA_ERROR);
-            } else if (tev) {
-                cudaEventRecord(tev[2], ps);
-            }
-            if (out_fused) *out_fused = fork ? 2 : 1;
-            d_logits = nullptr;                                // done (or in flight on the side stream)
+            mode = 0;                                          // a head shape its 25 KB do not hold: the two kernels, in stream
         }
     }
     if (d_frames) {
@@ -281,8 +340,19 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
         if ((rc = tk_b200_preprocess_batch(&b, st)) != TK_SUCCESS) return rc;
     }
     if (tev) cudaEventRecord(tev[1], st);
-    if (fork) TK_CUDA_TRY(cudaStreamWaitEvent(st, p->ev_join, 0), TK_ERROR_GPU_CUDA_ERROR);
-    if (d_logits) {
+    if (post_done) TK_CUDA_TRY(cudaStreamWaitEvent(st, p->ev_join, 0), TK_ERROR_GPU_CUDA_ERROR);
+    if (d_logits && !post_done && mode != 0) {
+        const tk_b200_post_params_t q = fused_params(mode == 2 ? 1 : 0);
+        rc = postprocess_fused_packed(&q, d_obj, st);
+        if (rc == TK_SUCCESS) {
+            post_done = true;
+            if (tev) cudaEventRecord(tev[2], st);
+            if (out_mode) *out_mode = 1;
+        } else if (rc != TK_ERROR_NOT_IMPLEMENTED) {
+            return rc;
+        }
+    }
+    if (d_logits && !post_done) {
         tk_b200_decode_params_t d{};
         d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
         d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
@@ -298,7 +368,7 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
             m.restore_in_width = c.tensor_width; m.restore_in_height = c.tensor_height;
         }
         if ((rc = tk_kernels_nms_classwise(&m, st)) != TK_SUCCESS) return rc;
-    } else if (tev && !fused) {
+    } else if (tev && !d_logits) {
         cudaEventRecord(tev[2], st);
     }
     if (tev) cudaEventRecord(tev[3], st);
@@ -313,6 +383,11 @@ extern "C" tk_error_code_t tk_b200_pipeline_process_device(tk_b200_pipeline_t* p
     if (n > p->cfg.max_batch) return TK_ERROR_BUFFER_TOO_SMALL;
     DevScope scope(p->cfg.device_id);
     if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    {
+        std::lock_guard<std::mutex> lk(p->thr_mu);
+        p->cfg.confidence_threshold = p->thr_conf;
+        p->cfg.iou_threshold = p->thr_iou;
+    }
     cudaEvent_t* tev = nullptr;
     uint8_t* mode = nullptr;
     if (p->timing_on && p->timing_calls < p->timing_cap) {
@@ -351,8 +426,8 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_timing(tk_b200_pipeline_t* p, 
 }
 
 // Sums of the recorded stage durations (ms): [0] pre-process, [1] decode, [2] NMS; *out_calls = calls recorded.
-// Calls that ran the fused post-process kernel: [1] = post_kernel (decode + NMS) from the fork to its end — it runs
-// beside the pre-process kernel, so [0] + [1] exceeds the step — and [2] = 0.  Waits for the recorded events.
+// Calls that ran a fused post-process kernel: [1] = decode + NMS together and [2] = 0 (the co-resident form, mode 2,
+// is timed from the fork: it runs beside the pre-process kernel, so [0] + [1] exceeds the step).  Waits for the events.
 extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, double ms_sum[3], uint32_t* out_calls) {
     if (!p || !ms_sum || !out_calls) return TK_ERROR_INVALID_ARGUMENT;
     DevScope scope(p->cfg.device_id);
@@ -365,8 +440,9 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
         if (p->timing_mode[c] != 0) {
             float a = 0.0f, b = 0.0f;
             TK_CUDA_TRY(cudaEventSynchronize(e[2]), TK_ERROR_GPU_SYNCHRONIZATION_FAILED);
-            if (p->timing_mode[c] == 2) TK_CUDA_TRY(cudaEventElapsedTime(&a, e[0], e[1]), TK_ERROR_GPU_CUDA_ERROR);
-            TK_CUDA_TRY(cudaEventElapsedTime(&b, e[0], e[2]), TK_ERROR_GPU_CUDA_ERROR);
+            TK_CUDA_TRY(cudaEventElapsedTime(&a, e[0], e[1]), TK_ERROR_GPU_CUDA_ERROR);
+            // fused in stream: behind the pre-process kernel; fused beside it: from the fork
+            TK_CUDA_TRY(cudaEventElapsedTime(&b, p->timing_mode[c] == 2 ? e[0] : e[1], e[2]), TK_ERROR_GPU_CUDA_ERROR);
             ms_sum[0] += (double)a; ms_sum[1] += (double)b;
             continue;
         }
@@ -378,8 +454,6 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
     }
     return TK_SUCCESS;
 }
-
-#define TK_PIPE_TRY(call) TK_CUDA_TRY(call, TK_ERROR_GPU_MEMORY_COPY_FAILED)
 
 // Host-buffer flow.
 //
@@ -396,14 +470,17 @@ extern "C" tk_error_code_t tk_b200_pipeline_stage_times(tk_b200_pipeline_t* p, d
 // moves ~50x more bytes over PCIe than the kernel needs.  When the caller's logits
 // are in page-locked host memory (tk_b200_host_alloc / cudaHostAlloc: device-
 // addressable under UVA) they stay there: the objectness column is packed into a
-// dense page-locked array by host threads while the frame copies run, uploaded as
-// one copy, and decode_kernel<PACKED> reads only the surviving rows in place over
+// dense page-locked array by the handle's host threads while the frame copies run,
+// uploaded as one copy, and the PACKED decode reads only the surviving rows in place over
 // PCIe (stage_host_logits = 2 or a batch of a frame or two: the objectness words are
 // read in place as well, one PCIe request per row).  One launch for the whole batch
 // on its own stream, concurrent with the frame uploads.  Pageable logits (or
 // stage_host_logits = 1) are staged through HBM chunk by chunk.
 //
 // Frames of a sparse geometry are not copied either (see frames_in_place below).
+//
+// Errors: nothing returns out of the middle — a failed enqueue sets rc, stops further enqueues and falls through to
+// the drain at the end, so no copy is left in flight on the caller's buffers when the call returns.
 static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_frames, const float* h_logits,
                                          const float* d_logits_all, uint32_t n, void* h_tensor,
                                          tk_b200_candidate_t* h_dets, uint32_t* h_ndets) {
@@ -416,10 +493,29 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
     if (n > p->cfg.max_batch) return TK_ERROR_BUFFER_TOO_SMALL;
     DevScope scope(p->cfg.device_id);
     if (!scope.ok) return TK_ERROR_GPU_DEVICE_SET_FAILED;
+    {   // thresholds as of now (tk_b200_pipeline_update_thresholds may run on another thread, as the reference's
+        // pipeline does under its mutex, src/vision/tk_vision_pipeline.c:131-150)
+        std::lock_guard<std::mutex> lk(p->thr_mu);
+        p->cfg.confidence_threshold = p->thr_conf;
+        p->cfg.iou_threshold = p->thr_iou;
+    }
     const size_t det_stride = p->cfg.max_detections;
     tk_error_code_t rc = TK_SUCCESS;
+    p->over_frames = 0; p->over_max = 0; p->counts_valid = 0;
+    // enqueue helper: false (and rc set, once) when the runtime refused
+    auto ok = [&](cudaError_t e, const char* what) {
+        if (e == cudaSuccess) return true;
+        if (rc == TK_SUCCESS) {
+            tk_error_set_detail("process_host: %s -> %s", what, cudaGetErrorString(e));
+            rc = TK_ERROR_GPU_MEMORY_COPY_FAILED;
+        }
+        cudaGetLastError();
+        return false;
+    };
 
-    // Whole-batch post-process when the logits are device-addressable where they lie.
+    // Whole-batch post-process when the logits are device-addressable where they lie.  The caller's d_logits (the
+    // _frames entry point) must be complete and visible to the device before the call: they are read on the
+    // pipeline's own streams, which nothing orders behind the stream that produced them.
     const float* logits_in_place = d_logits_all;
     bool pack_objectness = false;
     if (h_logits && p->cfg.stage_host_logits != 1) {
@@ -432,23 +528,17 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
             cudaGetLastError();
         }
     }
-    if (pack_objectness && (!p->h_obj || !p->d_obj)) {
-        const size_t ob = (size_t)p->cfg.max_batch * p->cfg.num_proposals * sizeof(float);
-        if ((!p->h_obj && cudaHostAlloc(reinterpret_cast<void**>(&p->h_obj), ob, cudaHostAllocDefault) != cudaSuccess) ||
-            (!p->d_obj && cudaMalloc(reinterpret_cast<void**>(&p->d_obj), ob) != cudaSuccess)) {
-            tk_error_set_detail("pipeline objectness staging: %s", cudaGetErrorString(cudaGetLastError()));
-            return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
-        }
-    }
-    auto post_in_place = [&](const float* d_obj) -> tk_error_code_t {
-        tk_error_code_t r = run_kernels(p, nullptr, logits_in_place, n, nullptr, p->d_cands, p->d_counts, p->d_dets, p->d_ndets,
-                                        p->s_post, nullptr, d_obj);
-        if (r != TK_SUCCESS) return r;
-        TK_PIPE_TRY(cudaMemcpyAsync(h_dets, p->d_dets, (size_t)n * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_post));
-        TK_PIPE_TRY(cudaMemcpyAsync(h_ndets, p->d_ndets, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post));
-        return TK_SUCCESS;
+    if (pack_objectness && (rc = ensure_pack_resources(p)) != TK_SUCCESS) return rc;
+    auto post_in_place = [&](const float* d_obj) {
+        const tk_error_code_t r = run_kernels(p, nullptr, logits_in_place, n, nullptr, p->d_cands, p->d_counts, p->d_dets, p->d_ndets,
+                                              p->s_post, nullptr, d_obj);
+        if (r != TK_SUCCESS) { if (rc == TK_SUCCESS) rc = r; return; }
+        if (!ok(cudaMemcpyAsync(h_dets, p->d_dets, (size_t)n * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_post), "detections D2H")) return;
+        if (!ok(cudaMemcpyAsync(h_ndets, p->d_ndets, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post), "counts D2H")) return;
+        if (ok(cudaMemcpyAsync(p->h_cand_counts, p->d_counts, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_post), "candidate counts D2H"))
+            p->counts_valid = n;
     };
-    if (logits_in_place && !pack_objectness) rc = post_in_place(nullptr);
+    if (logits_in_place && !pack_objectness) post_in_place(nullptr);
     // Frames: when the geometry only ever stages two source rows per output row (4K -> 640: 59 % of the luma rows) and
     // the frames are page-locked, the pre-process kernel's row ring pulls exactly those rows over PCIe in place —
     // fewer bytes cross the link than a copy of the frames would move (tools/exp_pre_zerocopy.py: 32 x 4K I420
@@ -463,15 +553,13 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
             cudaGetLastError();
         }
     }
-    if (frames_in_place) {
-        rc = run_kernels(p, frames_in_place, nullptr, n, p->d_tensor, nullptr, nullptr, nullptr, nullptr, p->s_compute);
+    if (frames_in_place && rc == TK_SUCCESS) {
+        const tk_error_code_t r = run_kernels(p, frames_in_place, nullptr, n, p->d_tensor, nullptr, nullptr, nullptr, nullptr, p->s_compute);
+        if (r != TK_SUCCESS) rc = r;
         if (rc == TK_SUCCESS && h_tensor) {
-            rc = [&]() -> tk_error_code_t {
-                TK_PIPE_TRY(cudaEventRecord(p->ev_computed[0], p->s_compute));
-                TK_PIPE_TRY(cudaStreamWaitEvent(p->s_down, p->ev_computed[0], 0));
-                TK_PIPE_TRY(cudaMemcpyAsync(h_tensor, p->d_tensor, (size_t)n * p->tensor_bytes, cudaMemcpyDeviceToHost, p->s_down));
-                return TK_SUCCESS;
-            }();
+            if (ok(cudaEventRecord(p->ev_computed[0], p->s_compute), "event record") &&
+                ok(cudaStreamWaitEvent(p->s_down, p->ev_computed[0], 0), "stream wait"))
+                ok(cudaMemcpyAsync(h_tensor, p->d_tensor, (size_t)n * p->tensor_bytes, cudaMemcpyDeviceToHost, p->s_down), "tensor D2H");
         }
         h_frames = nullptr;                       // done: the chunk loop below only has pageable logits left to stage
     }
@@ -482,64 +570,51 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
         const uint32_t f0 = k * p->chunk;
         const uint32_t m = (n - f0) < p->chunk ? (n - f0) : p->chunk;
         // ---- upload
-        if (k >= (uint32_t)kSlots) TK_PIPE_TRY(cudaStreamWaitEvent(p->s_up, p->ev_computed[s], 0));
-        if (h_frames)
-            TK_PIPE_TRY(cudaMemcpyAsync(p->d_frames[s], static_cast<const uint8_t*>(h_frames) + (size_t)f0 * p->frame_bytes,
-                                        (size_t)m * p->frame_bytes, cudaMemcpyHostToDevice, p->s_up));
-        if (chunk_logits)
-            TK_PIPE_TRY(cudaMemcpyAsync(p->d_logits[s], reinterpret_cast<const uint8_t*>(h_logits) + (size_t)f0 * p->logit_bytes,
-                                        (size_t)m * p->logit_bytes, cudaMemcpyHostToDevice, p->s_up));
-        TK_PIPE_TRY(cudaEventRecord(p->ev_uploaded[s], p->s_up));
+        if (k >= (uint32_t)kSlots && !ok(cudaStreamWaitEvent(p->s_up, p->ev_computed[s], 0), "stream wait")) break;
+        if (h_frames && !ok(cudaMemcpyAsync(p->d_frames[s], static_cast<const uint8_t*>(h_frames) + (size_t)f0 * p->frame_bytes,
+                                            (size_t)m * p->frame_bytes, cudaMemcpyHostToDevice, p->s_up), "frames H2D")) break;
+        if (chunk_logits && !ok(cudaMemcpyAsync(p->d_logits[s], reinterpret_cast<const uint8_t*>(h_logits) + (size_t)f0 * p->logit_bytes,
+                                                (size_t)m * p->logit_bytes, cudaMemcpyHostToDevice, p->s_up), "logits H2D")) break;
+        if (!ok(cudaEventRecord(p->ev_uploaded[s], p->s_up), "event record")) break;
         // ---- compute
-        TK_PIPE_TRY(cudaStreamWaitEvent(p->s_compute, p->ev_uploaded[s], 0));
-        rc = run_kernels(p, h_frames ? p->d_frames[s] : nullptr, chunk_logits ? p->d_logits[s] : nullptr, m,
-                         p->d_tensor + (size_t)f0 * p->tensor_bytes,
-                         p->d_cands + (size_t)f0 * p->cfg.max_candidates, p->d_counts + f0,
-                         p->d_dets + (size_t)f0 * det_stride, p->d_ndets + f0, p->s_compute);
-        if (rc != TK_SUCCESS) break;
-        TK_PIPE_TRY(cudaEventRecord(p->ev_computed[s], p->s_compute));
+        if (!ok(cudaStreamWaitEvent(p->s_compute, p->ev_uploaded[s], 0), "stream wait")) break;
+        const tk_error_code_t r = run_kernels(p, h_frames ? p->d_frames[s] : nullptr, chunk_logits ? p->d_logits[s] : nullptr, m,
+                                              p->d_tensor + (size_t)f0 * p->tensor_bytes,
+                                              p->d_cands + (size_t)f0 * p->cfg.max_candidates, p->d_counts + f0,
+                                              p->d_dets + (size_t)f0 * det_stride, p->d_ndets + f0, p->s_compute);
+        if (r != TK_SUCCESS) { rc = r; break; }
+        if (!ok(cudaEventRecord(p->ev_computed[s], p->s_compute), "event record")) break;
         // ---- download
-        if (chunk_logits || (h_tensor && h_frames)) TK_PIPE_TRY(cudaStreamWaitEvent(p->s_down, p->ev_computed[s], 0));
+        if ((chunk_logits || (h_tensor && h_frames)) && !ok(cudaStreamWaitEvent(p->s_down, p->ev_computed[s], 0), "stream wait")) break;
         if (chunk_logits) {
-            TK_PIPE_TRY(cudaMemcpyAsync(h_dets + (size_t)f0 * det_stride, p->d_dets + (size_t)f0 * det_stride,
-                                        (size_t)m * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_down));
-            TK_PIPE_TRY(cudaMemcpyAsync(h_ndets + f0, p->d_ndets + f0, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_down));
+            if (!ok(cudaMemcpyAsync(h_dets + (size_t)f0 * det_stride, p->d_dets + (size_t)f0 * det_stride,
+                                    (size_t)m * det_stride * sizeof(tk_b200_candidate_t), cudaMemcpyDeviceToHost, p->s_down), "detections D2H")) break;
+            if (!ok(cudaMemcpyAsync(h_ndets + f0, p->d_ndets + f0, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_down), "counts D2H")) break;
+            if (!ok(cudaMemcpyAsync(p->h_cand_counts + f0, p->d_counts + f0, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->s_down), "candidate counts D2H")) break;
+            p->counts_valid = f0 + m;
         }
-        if (h_tensor && h_frames)
-            TK_PIPE_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(h_tensor) + (size_t)f0 * p->tensor_bytes,
-                                        p->d_tensor + (size_t)f0 * p->tensor_bytes, (size_t)m * p->tensor_bytes,
-                                        cudaMemcpyDeviceToHost, p->s_down));
+        if (h_tensor && h_frames &&
+            !ok(cudaMemcpyAsync(static_cast<uint8_t*>(h_tensor) + (size_t)f0 * p->tensor_bytes,
+                                p->d_tensor + (size_t)f0 * p->tensor_bytes, (size_t)m * p->tensor_bytes,
+                                cudaMemcpyDeviceToHost, p->s_down), "tensor D2H")) break;
     }
     if (pack_objectness && rc == TK_SUCCESS) {
-        // The frame copies are queued; while the copy engine works through them, host threads pack the objectness
-        // word of every row (4 bytes out of 340) into the page-locked column, which then crosses PCIe as one dense
-        // copy instead of one read request per row (profiles/r1_pcie_inplace.md).  Pure data movement: the
-        // threshold, like everything else, is applied by decode_kernel.
+        // The frame copies are queued; while the copy engine works through them, the handle's host threads pack the
+        // objectness word of every row (4 bytes out of 340) into the page-locked column, which then crosses PCIe as
+        // one dense copy instead of one read request per row (profiles/r1_pcie_inplace.md).  Pure data movement: the
+        // threshold, like everything else, is applied on the device.
         const size_t P = p->cfg.num_proposals, L = 5 + (size_t)p->cfg.num_classes;
         const size_t rows = (size_t)n * P;
-        const unsigned hw = std::thread::hardware_concurrency();
-        const unsigned T = hw >= 16 ? 4u : (hw >= 4 ? 2u : 1u);
         float* dst = p->h_obj;
-        auto work = [=](unsigned t) {
-            const size_t a = rows * t / T, b = rows * (t + 1) / T;
+        p->pool->parallel_for([=](unsigned part, unsigned parts) {
+            const size_t a = rows * part / parts, b = rows * (part + 1) / parts;
             const float* sp = h_logits + a * L + 4;
             for (size_t r = a; r < b; ++r, sp += L) dst[r] = *sp;
-        };
-        std::vector<std::thread> pool;
-        unsigned started = 1;                                // range 0 is the caller's
-        try {
-            for (; started < T; ++started) pool.emplace_back(work, started);
-        } catch (...) {
-        }
-        work(0);
-        for (unsigned t = started; t < T; ++t) work(t);      // ranges whose thread could not be started
-        for (auto& th : pool) th.join();
-        rc = [&]() -> tk_error_code_t {
-            TK_PIPE_TRY(cudaMemcpyAsync(p->d_obj, p->h_obj, rows * sizeof(float), cudaMemcpyHostToDevice, p->s_post));
-            return post_in_place(p->d_obj);
-        }();
+        });
+        if (ok(cudaMemcpyAsync(p->d_obj, p->h_obj, rows * sizeof(float), cudaMemcpyHostToDevice, p->s_post), "objectness H2D"))
+            post_in_place(p->d_obj);
     }
-    // Drain even after an error so no copy is left in flight on the caller's buffers.
+    // Drain, also after an error: no copy stays in flight on the caller's buffers.
     cudaError_t es[4] = {cudaStreamSynchronize(p->s_up), cudaStreamSynchronize(p->s_compute),
                          cudaStreamSynchronize(p->s_down), cudaStreamSynchronize(p->s_post)};
     for (int i = 0; i < 4; ++i) {
@@ -549,6 +624,18 @@ static tk_error_code_t process_host_impl(tk_b200_pipeline_t* p, const void* h_fr
         }
     }
     cudaGetLastError();
+    if (rc == TK_SUCCESS) {
+        // rows over the confidence threshold per frame vs the cap the kernels hold (tk_b200_pipeline_candidate_overflow)
+        for (uint32_t i = 0; i < p->counts_valid; ++i) {
+            const uint32_t c = p->h_cand_counts[i];
+            if (c > p->cfg.max_candidates) ++p->over_frames;
+            if (c > p->over_max) p->over_max = c;
+        }
+        if (p->over_frames)
+            tk_error_set_detail("process_host: %u frame(s) had more rows over the confidence threshold (up to %u) than "
+                                "max_candidates %u; their lists were cut to the first %u rows before NMS",
+                                p->over_frames, p->over_max, p->cfg.max_candidates, p->cfg.max_candidates);
+    }
     return rc;
 }
 

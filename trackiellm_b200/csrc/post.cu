@@ -142,7 +142,9 @@ __global__ void __launch_bounds__(kPostThreads, 8) post_kernel(const PostK k) {
                     const uint32_t j = g * R + i;
                     if (j >= mine) break;
                     const uint32_t sidx = warp + kPostWarps * j, r = row_of(sidx);
+                    TK_DEV_ASSERT(sidx < n_out && r < d.P);
                     float* row = wst + (size_t)((g & 1u) * R + i) * d.L;
+                    TK_DEV_ASSERT(reinterpret_cast<uint8_t*>(row + d.L) <= dsm + nms_smem_bytes(kNmsSmall));
                     RowRegs q;
                     load_row<false>(d, row, lane, q);
                     // softmax: the exponentials overwrite the staged class logits in place (each lane reads word j before it writes it)
@@ -187,20 +189,25 @@ static tk_error_code_t launch_post(const PostK& k, uint32_t grid, size_t smem, c
     return launch_status("post_kernel");
 }
 
-size_t post_fused_workspace_bytes(uint32_t max_candidates, int sm_count) {
-    if (max_candidates <= kNmsSmall) return 0;
+static uint32_t post_scratch_pitch(uint32_t max_candidates) {
     uint32_t pitch = 1024;
     while (pitch < max_candidates) pitch <<= 1;
-    return (size_t)sm_count * nms_smem_bytes(pitch);
+    return pitch;
+}
+// layout 0 (cluster per frame): one work area per frame; layout 1 (persistent CTAs): one per CTA, at most one per SM
+size_t post_fused_workspace_bytes(uint32_t max_candidates, uint32_t num_frames, int layout, int sm_count) {
+    if (max_candidates <= kNmsSmall) return 0;
+    const uint32_t areas = layout == 0 ? num_frames : (num_frames < (uint32_t)sm_count ? num_frames : (uint32_t)sm_count);
+    return (size_t)areas * nms_smem_bytes(post_scratch_pitch(max_candidates));
 }
 
 }  // namespace tkb
 
 using namespace tkb;
 
-extern "C" size_t tk_b200_postprocess_fused_workspace_bytes(uint32_t max_candidates) {
+extern "C" size_t tk_b200_postprocess_fused_workspace_bytes(uint32_t max_candidates, uint32_t num_frames, int layout) {
     const DeviceInfo* dev = device_info();
-    return dev ? post_fused_workspace_bytes(max_candidates, dev->sm_count) : 0;
+    return dev ? post_fused_workspace_bytes(max_candidates, num_frames, layout, dev->sm_count) : 0;
 }
 
 tk_error_code_t tkb::postprocess_fused_packed(const tk_b200_post_params_t* p, const float* d_objectness, cudaStream_t stream) {
@@ -210,10 +217,7 @@ tk_error_code_t tkb::postprocess_fused_packed(const tk_b200_post_params_t* p, co
     if (p->num_frames == 0) return TK_SUCCESS;
     if (p->num_proposals == 0) return TK_ERROR_INVALID_DIMENSIONS;      // dims check of tk_object_detector.c:325-336
     if ((unsigned)p->activation > TK_B200_ACT_SOFTMAX) return TK_ERROR_INVALID_ARGUMENT;
-    if (p->max_candidates > kNmsMaxK) {
-        tk_error_set_detail("post: max_candidates %u exceeds %u", p->max_candidates, kNmsMaxK);
-        return TK_ERROR_NOT_IMPLEMENTED;
-    }
+    if (p->max_candidates > (1u << 30)) return TK_ERROR_INVALID_ARGUMENT;
     const DeviceInfo* dev = device_info();
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
     PostK k{};
@@ -235,16 +239,24 @@ tk_error_code_t tkb::postprocess_fused_packed(const tk_b200_post_params_t* p, co
         k.n.sy = (float)p->restore_src_height / (float)p->restore_in_height;
     }
     k.n.num_frames = p->num_frames;
+    if ((unsigned)p->layout > 1u) return TK_ERROR_INVALID_ARGUMENT;
     const uint32_t grid = p->num_frames < (uint32_t)dev->sm_count ? p->num_frames : (uint32_t)dev->sm_count;
     if (p->max_candidates > kNmsSmall) {
-        const size_t need = post_fused_workspace_bytes(p->max_candidates, dev->sm_count);
+        const size_t need = post_fused_workspace_bytes(p->max_candidates, p->num_frames, p->layout, dev->sm_count);
         if (!p->d_workspace || p->workspace_bytes < need || (reinterpret_cast<uintptr_t>(p->d_workspace) & 15u)) {
             tk_error_set_detail("post: workspace of %zu bytes (16-byte aligned) needed for max_candidates %u", need, p->max_candidates);
             return TK_ERROR_BUFFER_TOO_SMALL;
         }
         k.scratch = static_cast<uint8_t*>(p->d_workspace);
-        k.scratch_pitch = 1024;
-        while (k.scratch_pitch < p->max_candidates) k.scratch_pitch <<= 1;
+        k.scratch_pitch = post_scratch_pitch(p->max_candidates);
+    }
+    if (p->layout == 0) {
+        // a cluster of 8 CTAs per frame: decode_kernel with the NMS tail (decode.cu)
+        tk_b200_decode_params_t dp{};
+        dp.d_logits = p->d_logits; dp.num_frames = p->num_frames; dp.num_proposals = p->num_proposals; dp.num_classes = p->num_classes;
+        dp.confidence_threshold = p->confidence_threshold; dp.activation = p->activation;
+        dp.d_candidates = p->d_candidates; dp.d_counts = p->d_counts; dp.max_candidates = p->max_candidates;
+        return decode_nms_cluster(&dp, d_objectness, &k.n, k.scratch, k.scratch_pitch, stream);
     }
     // Dynamic shared memory: exactly the small NMS layout (25 KB) — what fits beside two pre-process CTAs.  The decode
     // phase takes its bitmap, prefix and row list out of it and stages rows in the rest.
@@ -268,6 +280,40 @@ tk_error_code_t tkb::postprocess_fused_packed(const tk_b200_post_params_t* p, co
         case TK_B200_ACT_SIGMOID: return launch_post<TK_B200_ACT_SIGMOID>(k, grid, smem, stream);
         default:                  return launch_post<TK_B200_ACT_SOFTMAX>(k, grid, smem, stream);
     }
+}
+
+// Decode + class-wise NMS of ONE frame with NO candidate cap: the reference keeps every row that passes the threshold
+// (calloc(num_proposals), src/vision/tk_object_detector.c:339-355).  The composed entry points (detect,
+// tk_b200_postprocess_detections) run the capped kernels first and come here only for a frame whose count exceeded the
+// cap: decode with room for all P rows, NMS through nms_global_kernel.  Stream-ordered scratch; asynchronous.
+tk_error_code_t tkb::postprocess_frame_uncapped(const float* d_logits, uint32_t P, uint32_t C, tk_b200_activation_e act,
+                                               float conf_thr, float iou_thr, uint32_t max_det, int class_agnostic,
+                                               const uint32_t restore[4], tk_b200_candidate_t* d_dets, uint32_t* d_ndets,
+                                               cudaStream_t st) {
+    uint8_t* buf = nullptr;
+    const size_t cand_bytes = ((size_t)P * sizeof(tk_b200_candidate_t) + 255) & ~(size_t)255;
+    if (cudaMallocAsync(reinterpret_cast<void**>(&buf), cand_bytes + 256, st) != cudaSuccess) {
+        tk_error_set_detail("uncapped post-process: %zu B: %s", cand_bytes + 256, cudaGetErrorString(cudaGetLastError()));
+        return TK_ERROR_GPU_MEMORY_ALLOCATION_FAILED;
+    }
+    tk_b200_candidate_t* d_c = reinterpret_cast<tk_b200_candidate_t*>(buf);
+    uint32_t* d_n = reinterpret_cast<uint32_t*>(buf + cand_bytes);
+    tk_b200_decode_params_t d{};
+    d.d_logits = d_logits; d.num_frames = 1; d.num_proposals = P; d.num_classes = C; d.confidence_threshold = conf_thr;
+    d.activation = act; d.d_candidates = d_c; d.d_counts = d_n; d.max_candidates = P;
+    tk_error_code_t rc = tk_kernels_decode_detections(&d, st);
+    if (rc == TK_SUCCESS) {
+        tk_b200_nms_params_t m{};
+        m.d_candidates = d_c; m.d_counts = d_n; m.num_frames = 1; m.max_candidates = P; m.iou_threshold = iou_thr;
+        m.max_detections = max_det; m.class_agnostic = class_agnostic; m.d_detections = d_dets; m.d_num_detections = d_ndets;
+        if (restore) {
+            m.restore_src_width = restore[0]; m.restore_src_height = restore[1];
+            m.restore_in_width = restore[2]; m.restore_in_height = restore[3];
+        }
+        rc = tk_kernels_nms_classwise(&m, st);
+    }
+    cudaFreeAsync(buf, st);
+    return rc;
 }
 
 extern "C" tk_error_code_t tk_kernels_postprocess_fused(const tk_b200_post_params_t* p, cudaStream_t stream) {

@@ -51,11 +51,13 @@ struct PreK {
     uint32_t u_slot_off, v_slot_off;   // I420 offsets inside a ring slot
     uint32_t tab_w;         // dst_w rounded up to 4
     uint32_t ring_off;      // byte offset of the ring in dynamic smem
-    uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty output rows in flight
+    uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty row groups in flight
+    uint32_t big;           // 1: 512-thread CTAs (three row groups), 0: 352-thread CTAs (two)
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
     uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
     float one;              // 1.0f at run time (see sum2)
+    unsigned long long cplane[3];   // byte offset of the tensor plane that SOURCE channel c is written to (BGR: 2 - c)
     TraceBuf trace;         // debug: per-CTA record (tk_b200_debug_trace), buf == nullptr when off
 };
 
@@ -146,23 +148,26 @@ __device__ __forceinline__ float blend_norm(const PreK& p, int c, float m1, floa
 // The same arithmetic for one channel of TWO neighbouring output pixels at once, in packed fp32
 // (FADD2 / FMUL2 / FFMA2, sm_100: two IEEE round-to-nearest lanes per issued instruction) — every
 // lane performs exactly the scalar sequence above, so the results are bit-identical to it.
+// The bytes arrive as m = 2^23 + p (magic_byte).  The reference's first products p*(1-xd), p*xd are formed as
+// fma(m, w, -2^23*w): -2^23*w is exact (a power-of-two scaling), so the fma computes m*w - 2^23*w = p*w exactly and
+// rounds ONCE — the same value as fmul(p, w) — and the four subtractions that would turn m back into p disappear.
+// cxd = -2^23*xd, comx = -2^23*(1-xd).
 template <bool EXACT>
 __device__ __forceinline__ float2 blend_norm2(const PreK& p, int c, float2 m1, float2 m2, float2 m3, float2 m4,
-                                              float2 xd, float2 omx, float yd, float omy) {
-    const float2 nb = f2s(-kBias);
+                                              float2 xd, float2 omx, float2 cxd, float2 comx, float yd, float omy) {
     if constexpr (EXACT) {
-        const float2 p1 = add2(m1, nb), p2 = add2(m2, nb), p3 = add2(m3, nb), p4 = add2(m4, nb);
         const float2 yd2 = f2s(yd), omy2 = f2s(omy);
-        const float2 t1 = mul2(mul2(p1, omx), omy2);
-        const float2 t2 = mul2(mul2(p2, xd), omy2);
-        const float2 t3 = mul2(mul2(p3, omx), yd2);
-        const float2 t4 = mul2(mul2(p4, xd), yd2);
+        const float2 t1 = mul2(fma2(m1, omx, comx), omy2);
+        const float2 t2 = mul2(fma2(m2, xd, cxd), omy2);
+        const float2 t3 = mul2(fma2(m3, omx, comx), yd2);
+        const float2 t4 = mul2(fma2(m4, xd, cxd), yd2);
         const float2 v = sum2(sum2(sum2(t1, t2, p.one), t3, p.one), t4, p.one);
         const float2 t = sum2(mul2(v, f2s(1.0f / 255.0f)), f2s(-p.mean[c]), p.one);        // x - mean == x + (-mean)
         const float2 q = mul2(t, f2s(p.rstd[c]));
         const float2 r = fma2(q, f2s(-p.stdv[c]), t);                                  // -q*std == q*(-std)
         return fma2(r, f2s(p.rstd[c]), q);
     } else {
+        const float2 nb = f2s(-kBias);
         const float2 top = fma2(xd, add2(m2, f2(-m1.x, -m1.y)), add2(m1, nb));
         const float2 bot = fma2(xd, add2(m4, f2(-m3.x, -m3.y)), add2(m3, nb));
         const float2 v = fma2(f2s(yd), add2(bot, f2(-top.x, -top.y)), top);
@@ -258,8 +263,34 @@ __device__ __forceinline__ __half2 lerp_pair_half(uint32_t tl, uint32_t tr, uint
 
 enum { AR_EXACT = 0, AR_FAST = 1, AR_HALF = 2 };
 
-template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
-__global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
+#ifdef TK_B200_CHECKED
+// The ring slot the consumer is about to read / has just read must hold exactly source row `row` of the frame.
+template <int FMT>
+__device__ __noinline__ void check_ring_row(const PreK& p, const uint8_t* base, int row, const uint8_t* slot, uint32_t lane) {
+    TK_DEV_ASSERT(row >= 0 && row < (int)p.src_h);
+    const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
+    const volatile uint8_t* g = base + (size_t)row * p.src_stride;
+    for (uint32_t i = lane; i < nb; i += 32) TK_DEV_ASSERT(slot[i] == g[i]);
+    if constexpr (FMT == FMT_I420) {
+        const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+        const volatile uint8_t* gu = base + p.u_off + (size_t)cr * p.chroma_pitch;
+        const volatile uint8_t* gv = base + p.v_off + (size_t)cr * p.chroma_pitch;
+        for (uint32_t i = lane; i < (p.src_w >> 1); i += 32) {
+            TK_DEV_ASSERT(slot[p.u_slot_off + i] == gu[i]);
+            TK_DEV_ASSERT(slot[p.v_slot_off + i] == gv[i]);
+        }
+    }
+}
+#endif
+
+// BIG: 512-thread CTAs (three row groups of 160 consumer threads + the producer warp) at <= 64 registers instead of
+// 352-thread CTAs (two row groups) at <= 93: 32 resident warps per SM instead of 22.
+template <int FMT, bool F16, int AR, bool LBOX, bool TMA, bool BIG>
+__global__ void __launch_bounds__(BIG ? 512 : 352, 2) preprocess_kernel(const PreK p) {
+    // Output rows a warp takes per iteration.  2 was built and measured (the row set-up and the column constants are then
+    // paid once per 8 pixels of a thread): 119.2 us against 112.1 us for 64 x 1080p EXACT -> fp16 — the longer release
+    // interval of the ring costs more than the shorter instruction stream gains.  The loop below stays written for any RPI.
+    constexpr int RPI = 1;
     constexpr bool EXACT = (AR == AR_EXACT);
     static_assert(AR != AR_HALF || (F16 && FMT != FMT_I420), "HALF arithmetic: fp16 output, RGB8/RGBA8 input");
     extern __shared__ __align__(128) uint8_t smem[];
@@ -388,129 +419,174 @@ __global__ void __launch_bounds__(352, 2) preprocess_kernel(const PreK p) {
 
     const uint32_t Q = p.tab_w >> 2;
     const size_t plane = (size_t)p.dst_w * p.dst_h;
+    constexpr uint32_t ESZ = F16 ? 2 : 4;
     uint32_t seq_base = 0;               // ring sequence number of the current item's first source row
 
+    // A warp takes RPI consecutive output rows per iteration (hb .. hb+RPI-1, then hb += RPI * ty).
     for (uint32_t f = f_first; f <= f_last; ++f) {
         uint32_t h0, h1; item_rows(f, h0, h1);
         int ylo, nrows; uint32_t a_first; item_src_rows(p, h0, h1, ylo, nrows, a_first);
-        for (uint32_t h = h0 + cy; h < h1; h += p.ty) {
-            const bool vin = !LBOX || (h - p.pad_top) < p.new_h;
-            float yd = 0.0f, omy = 1.0f;
-            const uint8_t* row0 = ring;
-            const uint8_t* row1 = ring;
-            if (vin) {
-                float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
-                int y = min(__float2int_rz(gy), (int)p.src_h - 2);
-                yd = __fsub_rn(gy, (float)y);
-                omy = __fsub_rn(1.0f, yd);
-                const uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
-                if (rel != q0) pass_to(q0);
-                row0 = ring + (size_t)(q0 & smask) * p.slot_bytes;
-                row1 = ring + (size_t)(q1 & smask) * p.slot_bytes;
-                while (*staged <= q1) __nanosleep(32);
-                __threadfence_block();
-                mbar_wait_backoff(&full[q0 & smask], (q0 >> p.s_log2) & 1u);
-                mbar_wait_backoff(&full[q1 & smask], (q1 >> p.s_log2) & 1u);
+        for (uint32_t hb = h0 + RPI * cy; hb < h1; hb += RPI * p.ty) {
+            bool vin[RPI];
+            float yd[RPI], omy[RPI];
+            const uint8_t* row0[RPI];
+            const uint8_t* row1[RPI];
+            uint8_t* rowp[RPI];                  // byte address of the output row in tensor plane 0 of frame f
+            bool released = false;
+#ifdef TK_B200_CHECKED
+            int ysrc[RPI];
+#endif
+#pragma unroll
+            for (int r = 0; r < RPI; ++r) {
+                const uint32_t h = hb + r;
+                vin[r] = h < h1 && (!LBOX || (h - p.pad_top) < p.new_h);
+                yd[r] = 0.0f; omy[r] = 1.0f;
+                row0[r] = ring; row1[r] = ring;
+                rowp[r] = static_cast<uint8_t*>(p.out) + ((size_t)f * 3 * plane + (size_t)h * p.dst_w) * ESZ;
+                if (vin[r]) {
+                    float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
+                    int y = min(__float2int_rz(gy), (int)p.src_h - 2);
+                    yd[r] = __fsub_rn(gy, (float)y);
+                    omy[r] = __fsub_rn(1.0f, yd[r]);
+                    const uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
+                    // release what lies below the FIRST row of the group only: the later rows read at or above it
+                    if (!released) { if (rel != q0) pass_to(q0); released = true; }
+                    row0[r] = ring + (size_t)(q0 & smask) * p.slot_bytes;
+                    row1[r] = ring + (size_t)(q1 & smask) * p.slot_bytes;
+                    while (*staged <= q1) __nanosleep(32);
+                    __threadfence_block();
+                    mbar_wait_backoff(&full[q0 & smask], (q0 >> p.s_log2) & 1u);
+                    mbar_wait_backoff(&full[q1 & smask], (q1 >> p.s_log2) & 1u);
+#ifdef TK_B200_CHECKED
+                    ysrc[r] = y;
+                    TK_DEV_ASSERT(q1 < *staged && q0 >= rel && q1 - rel < S);        // inside the window this warp holds
+                    TK_DEV_ASSERT((size_t)(q1 & smask) * p.slot_bytes + p.slot_bytes <= (size_t)S * p.slot_bytes);
+                    check_ring_row<FMT>(p, frame_ptr(f), y, row0[r], lane);
+                    check_ring_row<FMT>(p, frame_ptr(f), y + 1, row1[r], lane);
+#endif
+                }
             }
             for (uint32_t q = cx; q < Q; q += p.tx) {
+                const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+                const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
                 if constexpr (AR == AR_HALF) {
-                    const __half2 yd2 = __float2half2_rn(yd);
+                    const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
+                    const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
                     const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
                     const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
-                    uint32_t org[4], obb[4];
-                    if (vin) {
-                        const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
-                        const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
-                        const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
-                        const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
-                            uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
-                            fetch_pairs_half<FMT>(row0, xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
-                            fetch_pairs_half<FMT>(row1, xbs[j], bl_rg, bl_bb, br_rg, br_bb);
-                            const __half2 xd2 = as_h2(xds[j]);
-                            org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                            obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
-                        }
-                    } else {
+                    for (int r = 0; r < RPI; ++r) {
+                        if (hb + r >= h1) break;
+                        const __half2 yd2 = __float2half2_rn(yd[r]);
+                        uint32_t org[4], obb[4];
+                        if (vin[r]) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
-                    }
-                    // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
-                    const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
-                    const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
-                    const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
-                    const size_t pix = (size_t)h * p.dst_w + 4u * q;
-                    __half* outp = static_cast<__half*>(p.out);
-                    const uint2 vs[3] = {vr, vg, vb};
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const size_t e = ((size_t)f * 3 + (p.swap_rb ? 2 - c : c)) * plane + pix;
-                        if (p.vec_store) {
-                            __stcs(reinterpret_cast<uint2*>(outp + e), vs[c]);
+                            for (int j = 0; j < 4; ++j) {
+                                if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
+                                uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
+                                fetch_pairs_half<FMT>(row0[r], xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
+                                fetch_pairs_half<FMT>(row1[r], xbs[j], bl_rg, bl_bb, br_rg, br_bb);
+                                const __half2 xd2 = as_h2(xds[j]);
+                                org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                                obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                            }
                         } else {
-                            const uint32_t wds[2] = {vs[c].x, vs[c].y};
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (4u * q + j < p.dst_w)
-                                    reinterpret_cast<uint16_t*>(outp)[e + j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                            for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
                         }
-                    }
-                    continue;
-                }
-                float o[3][4];
-                if (vin) {
-                    const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
-                    const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
-                    const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
-                    const float xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+                        // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
+                        const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
+                        const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
+                        const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
+                        uint8_t* qp = rowp[r] + (size_t)(4u * q) * 2;
+                        const uint2 vs[3] = {vr, vg, vb};
+                        if (p.vec_store) {
 #pragma unroll
-                    for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
-                        float ma[4][3], mb[4][3];
-                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j], 0) : xbs[j], ma);
-                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
-                        const float2 xd2 = f2(xds[j], xds[j + 1]);
-                        const float2 omx2 = add2(f2s(1.0f), f2(-xd2.x, -xd2.y));      // 1 - xd
+                            for (int c = 0; c < 3; ++c) __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), vs[c]);
+                        } else {
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            const float2 r = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
-                                                                f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2, omx2, yd, omy);
-                            o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : r.x;
-                            o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : r.y;
+                            for (int c = 0; c < 3; ++c) {
+                                const uint32_t wds[2] = {vs[c].x, vs[c].y};
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    if (4u * q + j < p.dst_w)
+                                        reinterpret_cast<uint16_t*>(qp + p.cplane[c])[j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                            }
                         }
                     }
                 } else {
+                    const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
+                    // column constants of the quad, as two packed pairs: xd, 1 - xd, and (EXACT) their -2^23 multiples
+                    float2 xd2[2] = {f2(xd4.x, xd4.y), f2(xd4.z, xd4.w)}, omx2[2], cxd2[2], comx2[2];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
-                }
-                const size_t pix = (size_t)h * p.dst_w + 4u * q;
+                    for (int jp = 0; jp < 2; ++jp) {
+                        omx2[jp] = add2(f2s(1.0f), f2(-xd2[jp].x, -xd2[jp].y));      // 1 - xd
+                        cxd2[jp] = xd2[jp]; comx2[jp] = omx2[jp];
+                        if constexpr (EXACT) { cxd2[jp] = mul2(xd2[jp], f2s(-kBias)); comx2[jp] = mul2(omx2[jp], f2s(-kBias)); }
+                    }
 #pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const size_t e = ((size_t)f * 3 + (p.swap_rb ? 2 - c : c)) * plane + pix;
-                    if (p.vec_store) {
-                        if constexpr (F16) {
-                            __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
-                            __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
-                            uint2 v;
-                            v.x = *reinterpret_cast<uint32_t*>(&lo);
-                            v.y = *reinterpret_cast<uint32_t*>(&hi);
-                            __stcs(reinterpret_cast<uint2*>(static_cast<__half*>(p.out) + e), v);
+                    for (int r = 0; r < RPI; ++r) {
+                        if (hb + r >= h1) break;
+                        float o[3][4];
+                        if (vin[r]) {
+#pragma unroll
+                            for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
+                                float ma[4][3], mb[4][3];
+                                fetch_quad<FMT>(p, row0[r], row1[r], LBOX ? max(xbs[j], 0) : xbs[j], ma);
+                                fetch_quad<FMT>(p, row0[r], row1[r], LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
+#pragma unroll
+                                for (int c = 0; c < 3; ++c) {
+                                    const float2 v = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
+                                                                        f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2[j >> 1],
+                                                                        omx2[j >> 1], cxd2[j >> 1], comx2[j >> 1], yd[r], omy[r]);
+                                    o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : v.x;
+                                    o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : v.y;
+                                }
+                            }
                         } else {
-                            __stcs(reinterpret_cast<float4*>(static_cast<float*>(p.out) + e),
-                                   make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
-                        }
-                    } else {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (4u * q + j < p.dst_w) {
-                                if constexpr (F16) static_cast<__half*>(p.out)[e + j] = __float2half_rn(o[c][j]);
-                                else static_cast<float*>(p.out)[e + j] = o[c][j];
+                            for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
+                        }
+                        // one 64-bit address per quad; the channel planes are constant byte offsets from it
+                        uint8_t* qp = rowp[r] + (size_t)(4u * q) * ESZ;
+                        if (p.vec_store) {
+#pragma unroll
+                            for (int c = 0; c < 3; ++c) {
+                                if constexpr (F16) {
+                                    __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
+                                    __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
+                                    uint2 v;
+                                    v.x = *reinterpret_cast<uint32_t*>(&lo);
+                                    v.y = *reinterpret_cast<uint32_t*>(&hi);
+                                    __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), v);
+                                } else {
+                                    __stcs(reinterpret_cast<float4*>(qp + p.cplane[c]), make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < 3; ++c) {
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    if (4u * q + j < p.dst_w) {
+                                        if constexpr (F16) reinterpret_cast<__half*>(qp + p.cplane[c])[j] = __float2half_rn(o[c][j]);
+                                        else reinterpret_cast<float*>(qp + p.cplane[c])[j] = o[c][j];
+                                    }
+                                }
                             }
                         }
                     }
                 }
             }
+#ifdef TK_B200_CHECKED
+            // ... and still hold them now that every pixel of the group has been computed (nothing overwrote a slot early)
+#pragma unroll
+            for (int r = 0; r < RPI; ++r)
+                if (vin[r]) {
+                    check_ring_row<FMT>(p, frame_ptr(f), ysrc[r], row0[r], lane);
+                    check_ring_row<FMT>(p, frame_ptr(f), ysrc[r] + 1, row1[r], lane);
+                }
+#endif
         }
         seq_base += (uint32_t)nrows;
     }
@@ -557,7 +633,7 @@ void letterbox_geometry(uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh,
 
 template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 static tk_error_code_t launch_variant(const PreK& k, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
-    auto kern = preprocess_kernel<FMT, F16, AR, LBOX, TMA>;
+    auto kern = k.big ? preprocess_kernel<FMT, F16, AR, LBOX, TMA, true> : preprocess_kernel<FMT, F16, AR, LBOX, TMA, false>;
     TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     // Largest shared-memory carve-out, like post_kernel (post.cu), which the pipeline runs beside this kernel: with one
     // L1 / shared split for both, an SM never drains to reconfigure between them.
@@ -671,6 +747,8 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     k.y_ratio = ((float)k.src_h - 1.0f) / (float)k.new_h;
     k.swap_rb = bgr ? 1u : 0u;
     k.one = 1.0f;
+    for (int c = 0; c < 3; ++c)
+        k.cplane[c] = (unsigned long long)(bgr ? 2 - c : c) * k.dst_w * k.dst_h * (prm->output_type == TK_B200_OUT_F16 ? 2u : 4u);
     k.trace = trace_target();
     for (int c = 0; c < 3; ++c) {
         // constants are indexed by SOURCE channel; BGR byte c is tensor channel 2 - c
@@ -732,7 +810,10 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     // one more warp produces.
     const uint32_t Q = k.tab_w / 4;
     uint32_t tx = Q >= 160 ? 160 : ((Q + 31) & ~31u);
-    uint32_t ty = 320 / tx; if (ty < 1) ty = 1;
+    // TK_B200_PRE_BIG=1: 512-thread CTAs (A/B measurements; the default is what measured faster)
+    static const int big_env = [] { const char* e = getenv("TK_B200_PRE_BIG"); return e ? atoi(e) : 0; }();
+    k.big = (big_env == 1 && tx == 160) ? 1u : 0u;
+    uint32_t ty = (k.big ? 480 : 320) / tx; if (ty < 1) ty = 1;
 
     // Ring depth: the largest power of two (<= 32 slots) that fits the budget — two CTAs
     // per SM when that still covers the source rows `ty` consecutive output rows span plus

@@ -37,8 +37,18 @@ bool preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t* prm
 // page-locked host memory: pass 1 reads HBM, only the surviving rows cross PCIe.
 tk_error_code_t decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream);
 
+// decode.cu: decode_kernel with the NMS tail (layout 0 of tk_kernels_postprocess_fused); nms_k points at a filled NmsK.
+tk_error_code_t decode_nms_cluster(const tk_b200_decode_params_t* p, const float* d_objectness, const void* nms_k,
+                                   void* scratch, uint32_t scratch_pitch, cudaStream_t stream);
+
 // post.cu: tk_kernels_postprocess_fused with the objectness column supplied densely (see decode_detections_packed).
 tk_error_code_t postprocess_fused_packed(const tk_b200_post_params_t* p, const float* d_objectness, cudaStream_t stream);
+
+// post.cu: decode + NMS of one frame with no candidate cap (see the definition).
+tk_error_code_t postprocess_frame_uncapped(const float* d_logits, uint32_t P, uint32_t C, tk_b200_activation_e act,
+                                           float conf_thr, float iou_thr, uint32_t max_det, int class_agnostic,
+                                           const uint32_t restore[4], tk_b200_candidate_t* d_dets, uint32_t* d_ndets,
+                                           cudaStream_t st);
 
 // Number of kernels this library has enqueued (every launcher goes through
 // launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
@@ -62,6 +72,24 @@ inline tk_error_code_t launch_status(const char* what) {
     count_launch();
     return TK_SUCCESS;
 }
+
+// CHECKED build (make -C trackiellm_b200/csrc checked -> libtk_b200_checked.so, selected with TK_B200_LIB): device-side
+// assertions on every hand-computed shared-memory index / global offset, and — in the pre-process kernel — a byte-for-
+// byte comparison of every ring slot a consumer is about to read (and has just read) with the source row in global
+// memory, which turns any race of the producer / consumer protocol (a slot overwritten early, read before it landed,
+// a phase mix-up) into a trap.  compute-sanitizer is closed on this GPU pool; this is what stands in for
+// memcheck / racecheck (profiles/r2_sanitizer.md).  The shipped library is built without it.
+#ifdef TK_B200_CHECKED
+#define TK_DEV_ASSERT(cond)                                                                          \
+    do {                                                                                             \
+        if (!(cond)) {                                                                               \
+            printf("TK_B200_CHECKED %s:%d block %u thread %u: %s\n", __FILE__, __LINE__, blockIdx.x, threadIdx.x, #cond); \
+            __trap();                                                                                \
+        }                                                                                            \
+    } while (0)
+#else
+#define TK_DEV_ASSERT(cond) ((void)0)
+#endif
 
 #ifdef __CUDACC__
 __device__ __forceinline__ unsigned long long gtimer() {

@@ -144,8 +144,9 @@ def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float
 
 def postprocess_fused(logits: torch.Tensor, conf_thr: float, iou_thr: float, max_detections: int, *, act: int = ACT_RAW,
                       max_candidates: int = 4096, class_agnostic: bool = False,
-                      restore: tuple[int, int, int, int] | None = None):
-    """tk_kernels_postprocess_fused: decode + class-wise NMS per frame in one kernel.
+                      restore: tuple[int, int, int, int] | None = None, layout: int = 0):
+    """tk_kernels_postprocess_fused: decode + class-wise NMS per frame in one kernel (layout 0: a cluster of 8 CTAs
+    per frame; 1: persistent co-resident CTAs).
     -> (candidates, counts, detections, num_detections) as decode_detections / nms_classwise return them."""
     _require_cuda(logits, "logits")
     n, p, l = logits.shape
@@ -157,11 +158,11 @@ def postprocess_fused(logits: torch.Tensor, conf_thr: float, iou_thr: float, max
     L = capi.lib()
     L.tk_b200_postprocess_fused_workspace_bytes.restype = C.c_size_t
     with torch.cuda.device(dev):
-        need = int(L.tk_b200_postprocess_fused_workspace_bytes(C.c_uint32(max_candidates)))
+        need = int(L.tk_b200_postprocess_fused_workspace_bytes(C.c_uint32(max_candidates), C.c_uint32(n), C.c_int(layout)))
         ws = torch.empty((need,), dtype=torch.uint8, device=dev) if need else None
         prm = capi.PostParams(logits.data_ptr(), n, p, l - 5, conf_thr, act, cands.data_ptr(), counts.data_ptr(),
                               max_candidates, iou_thr, max_detections, int(class_agnostic), dets.data_ptr(),
-                              ndets.data_ptr(), *(restore or (0, 0, 0, 0)), ws.data_ptr() if ws is not None else None, need)
+                              ndets.data_ptr(), *(restore or (0, 0, 0, 0)), ws.data_ptr() if ws is not None else None, need, layout)
         capi.check(L.tk_kernels_postprocess_fused(C.byref(prm), _stream()), "tk_kernels_postprocess_fused")
         if ws is not None:
             ws.record_stream(torch.cuda.current_stream())
@@ -388,18 +389,13 @@ class Pipeline:
                  act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
                  max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False,
                  stage_host_logits: int = 0, fuse_postprocess: int = 0):
-        f16 = out_dtype == torch.float16
-        if arith is None:
-            arith = ARITH_EXACT                        # the reference's arithmetic; HALF / FAST are opt-in
-        self.cfg = capi.PipelineConfig(
-            device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, input_width=width,
-            input_height=height, input_stride_bytes=stride, input_format=fmt, tensor_width=tensor_w,
-            tensor_height=tensor_h, tensor_type=OUT_F16 if f16 else OUT_F32, resize_mode=resize, arith=arith,
-            pad_value=pad_value, mean=_f3(mean), std_dev=_f3(std), num_proposals=num_proposals,
-            num_classes=num_classes, activation=act, confidence_threshold=conf_thr, iou_threshold=iou_thr,
-            max_candidates=max_candidates, max_detections=max_detections, class_agnostic=int(class_agnostic),
-            restore_coordinates=int(restore_coordinates), stage_host_logits=int(stage_host_logits),
-            fuse_postprocess=int(fuse_postprocess))
+        self.cfg = self._make_config(
+            device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, width=width, height=height, stride=stride,
+            fmt=fmt, tensor_w=tensor_w, tensor_h=tensor_h, out_dtype=out_dtype, resize=resize, arith=arith,
+            pad_value=pad_value, mean=mean, std=std, num_proposals=num_proposals, num_classes=num_classes, act=act,
+            conf_thr=conf_thr, iou_thr=iou_thr, max_candidates=max_candidates, max_detections=max_detections,
+            class_agnostic=class_agnostic, restore_coordinates=restore_coordinates, stage_host_logits=stage_host_logits,
+            fuse_postprocess=fuse_postprocess)
         self.out_dtype = out_dtype
         self.device = torch.device("cuda", device_id)
         self._h = C.c_void_p()
@@ -412,6 +408,27 @@ class Pipeline:
         self.frame_bytes = int(L.tk_b200_pipeline_frame_bytes(self._h))
         self.tensor_bytes = int(L.tk_b200_pipeline_tensor_bytes(self._h))
         self.max_detections = max_detections or 500
+
+    def _make_config(self, *, device_id: int = 0, max_batch: int = 64, chunk_frames: int = 0,
+                     width: int = 1920, height: int = 1080, stride: int = 0, fmt: int = PIXEL_RGB8,
+                     tensor_w: int = 640, tensor_h: int = 640, out_dtype: torch.dtype = torch.float16,
+                     resize: int = RESIZE_STRETCH, arith: int | None = None, pad_value: float = 114.0,
+                     mean=IMAGENET_MEAN, std=IMAGENET_STD, num_proposals: int = 25200, num_classes: int = 80,
+                     act: int = ACT_RAW, conf_thr: float = 0.5, iou_thr: float = 0.5, max_candidates: int = 4096,
+                     max_detections: int = 500, class_agnostic: bool = False, restore_coordinates: bool = False,
+                     stage_host_logits: int = 0, fuse_postprocess: int = 0) -> "capi.PipelineConfig":
+        f16 = out_dtype == torch.float16
+        if arith is None:
+            arith = ARITH_EXACT                        # the reference's arithmetic; HALF / FAST are opt-in
+        return capi.PipelineConfig(
+            device_id=device_id, max_batch=max_batch, chunk_frames=chunk_frames, input_width=width,
+            input_height=height, input_stride_bytes=stride, input_format=fmt, tensor_width=tensor_w,
+            tensor_height=tensor_h, tensor_type=OUT_F16 if f16 else OUT_F32, resize_mode=resize, arith=arith,
+            pad_value=pad_value, mean=_f3(mean), std_dev=_f3(std), num_proposals=num_proposals,
+            num_classes=num_classes, activation=act, confidence_threshold=conf_thr, iou_threshold=iou_thr,
+            max_candidates=max_candidates, max_detections=max_detections, class_agnostic=int(class_agnostic),
+            restore_coordinates=int(restore_coordinates), stage_host_logits=int(stage_host_logits),
+            fuse_postprocess=int(fuse_postprocess))
 
     def close(self) -> None:
         if self._h:
@@ -426,6 +443,13 @@ class Pipeline:
     def update_thresholds(self, conf_thr: float, iou_thr: float) -> None:
         capi.check(capi.lib().tk_b200_pipeline_update_thresholds(self._h, C.c_float(conf_thr), C.c_float(iou_thr)),
                    "tk_b200_pipeline_update_thresholds")
+
+    def candidate_overflow(self) -> tuple[int, int]:
+        """(frames of the last process_host call cut to max_candidates, largest count of rows over the threshold)."""
+        a, b = C.c_uint32(0), C.c_uint32(0)
+        capi.check(capi.lib().tk_b200_pipeline_candidate_overflow(self._h, C.byref(a), C.byref(b)),
+                   "tk_b200_pipeline_candidate_overflow")
+        return int(a.value), int(b.value)
 
     def stage_timing(self, max_calls: int) -> None:
         capi.check(capi.lib().tk_b200_pipeline_stage_timing(self._h, C.c_uint32(max_calls)), "tk_b200_pipeline_stage_timing")
@@ -469,6 +493,62 @@ class Pipeline:
         fn = capi.lib().tk_b200_pipeline_process_host_frames if logits_on_device else capi.lib().tk_b200_pipeline_process_host
         capi.check(fn(self._h, hp(frames), hp(logits), C.c_uint32(n), hp(tensor), hp(dets), hp(counts)),
                    "tk_b200_pipeline_process_host")
+
+
+class Shard:
+    """tk_b200_shard_*: one process, one host thread + one pipeline per device, frames sharded by contiguous block
+    (SURVEY §8e).  device_ids may repeat an id (two pipelines on one device).  Keyword arguments as Pipeline
+    (max_batch = the whole job's batch)."""
+
+    def __init__(self, device_ids, **pipeline_kwargs):
+        # build the config through a throw-away Pipeline-like path without creating a pipeline
+        probe = Pipeline.__new__(Pipeline)
+        cfg = Pipeline._make_config(probe, **pipeline_kwargs)
+        self.cfg = cfg
+        self.max_detections = cfg.max_detections or 500
+        self.out_dtype = pipeline_kwargs.get("out_dtype", torch.float16)
+        ids = (C.c_int * len(device_ids))(*device_ids)
+        self._h = C.c_void_p()
+        capi.check(capi.lib().tk_b200_shard_create(C.byref(self._h), ids, C.c_uint32(len(device_ids)), C.byref(cfg)),
+                   "tk_b200_shard_create")
+
+    def close(self) -> None:
+        if self._h:
+            capi.lib().tk_b200_shard_destroy(C.byref(self._h))
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def update_thresholds(self, conf_thr: float, iou_thr: float) -> None:
+        capi.check(capi.lib().tk_b200_shard_update_thresholds(self._h, C.c_float(conf_thr), C.c_float(iou_thr)),
+                   "tk_b200_shard_update_thresholds")
+
+    def process_host(self, frames, logits, dets, counts, tensor=None) -> None:
+        def hp(t):
+            if t is None:
+                return None
+            return C.c_void_p(t.data_ptr() if isinstance(t, torch.Tensor) else t.ctypes.data)
+        n = frames.shape[0] if frames is not None else logits.shape[0]
+        capi.check(capi.lib().tk_b200_shard_process_host(self._h, hp(frames), hp(logits), C.c_uint32(n), hp(tensor), hp(dets),
+                                                         hp(counts)), "tk_b200_shard_process_host")
+
+    def gather(self, dets, counts):
+        """Final host gather -> (flat records [total,7] int32, offsets uint64[n+1])."""
+        d = dets.numpy() if isinstance(dets, torch.Tensor) else dets
+        c = (counts.numpy() if isinstance(counts, torch.Tensor) else counts).astype(np.uint32)
+        n = d.shape[0]
+        offs = np.zeros(n + 1, np.uint64)
+        L = capi.lib()
+        capi.check(L.tk_b200_shard_gather(None, c.ctypes.data_as(C.c_void_p), C.c_uint32(n), C.c_uint32(d.shape[1]), None,
+                                          offs.ctypes.data_as(C.c_void_p)), "tk_b200_shard_gather")
+        flat = np.zeros((int(offs[-1]), CAND_WORDS), np.int32)
+        capi.check(L.tk_b200_shard_gather(np.ascontiguousarray(d).ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p), C.c_uint32(n),
+                                          C.c_uint32(d.shape[1]), flat.ctypes.data_as(C.c_void_p), offs.ctypes.data_as(C.c_void_p)),
+                   "tk_b200_shard_gather")
+        return flat, offs
 
 
 class ObjectDetector:
