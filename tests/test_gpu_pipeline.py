@@ -273,3 +273,33 @@ def test_shard_harness_from_c(tmp_path):
         want += len(O.nms_classwise(c, 0.5, 300))
     assert total == want > 0
     print(out.stdout.strip())
+
+
+@pytest.mark.parametrize("act", [V.ACT_RAW, V.ACT_SIGMOID, V.ACT_SOFTMAX])
+@pytest.mark.parametrize("p,n", [(31, 3), (2000, 5), (25200, 2), (4097, 70)])
+def test_scan_inside_preprocess_equals_plain_decode(act, p, n, monkeypatch):
+    """TK_B200_SCAN=1: process_device runs decode's pass 1 (objectness threshold -> ballot words) in an extra warp of every
+    pre-process CTA and decode_kernel loads the words (measured slower, off by default).  Same detections, counts and
+    tensors either way and against the oracle — ragged proposal counts (words that straddle nothing: per-frame bitmaps),
+    more frames than fit one CTA's slice, every activation."""
+    frames = np.stack([synth.rgb_frame(W, H, 900 + i) for i in range(min(n, 6))])
+    frames = frames[np.arange(n) % len(frames)]
+    logits = np.stack([synth.logits_tensor(900 + i, num_proposals=p, objects=10, dups=5, adversarial=(i == 0 and p >= 64),
+                                           as_logit=(act != V.ACT_RAW)) for i in range(min(n, 6))])
+    logits = logits[np.arange(n) % len(logits)]
+    outs = []
+    for scan in ("1", "0"):
+        monkeypatch.setenv("TK_B200_SCAN", scan)
+        with make_pipe(n, num_proposals=p, act=act) as pipe:
+            dt, dd, dc = pipe.alloc_outputs(n)
+            df, dl = torch.from_numpy(frames).cuda(), torch.from_numpy(logits).cuda()
+            for _ in range(2):
+                pipe.process_device(df, dl, dt, dd, dc)
+            torch.cuda.synchronize()
+            outs.append((dt.cpu().numpy().copy(), V.candidates_to_numpy(dd, dc)))
+    assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
+    for i in range(n):
+        assert outs[0][1][i].tobytes() == outs[1][1][i].tobytes(), i
+    for i in range(min(n, 6)):
+        c, _ = O.decode(logits[i], 0.5, act, cap=4096)
+        assert outs[0][1][i].tobytes() == O.nms_classwise(c, 0.5, 500).view(V.CAND_DTYPE).tobytes()

@@ -62,6 +62,12 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
 
     // ---- pass 1: objectness threshold, ballot bitmap ------------------------
     asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // "I am resident" (waited on before DSMEM)
+    if (k.bitmap) {
+        // pass 1 was done by the scanner warps of the pre-process kernel: this CTA's slice of the frame's ballot words
+        const uint32_t wbase = row0 >> 5;                          // row0 is a multiple of 32
+        for (uint32_t i = tid; i < k.nwords; i += kDecThreads)
+            flags[i] = wbase + i < k.nwf ? k.bitmap[(size_t)frame * k.nwf + wbase + i] : 0u;
+    } else
     for (uint32_t base = 0; base < k.rows_per_cta; base += kDecUnroll * kDecThreads) {
         float obj[kDecUnroll];
 #pragma unroll
@@ -219,7 +225,7 @@ static tk_error_code_t launch_decode(const DecK& k, const NmsTail* tail, uint32_
 }
 
 static tk_error_code_t decode_launch_common(const tk_b200_decode_params_t* p, const float* d_objectness, const NmsTail* tail,
-                                            cudaStream_t stream) {
+                                            cudaStream_t stream, const uint32_t* d_bitmap = nullptr) {
     if (!p || !p->d_logits || !p->d_counts || (!p->d_candidates && p->max_candidates)) return TK_ERROR_INVALID_ARGUMENT;
     if (p->num_frames == 0) return TK_SUCCESS;
     if (p->num_proposals == 0) return TK_ERROR_INVALID_DIMENSIONS;      // dims check of tk_object_detector.c:325-336
@@ -228,6 +234,7 @@ static tk_error_code_t decode_launch_common(const tk_b200_decode_params_t* p, co
     if (!dev) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
     DecK k{};
     k.logits = p->d_logits; k.obj = d_objectness; k.cands = p->d_candidates; k.counts = p->d_counts;
+    k.bitmap = d_bitmap; k.nwf = (p->num_proposals + 31) / 32;
     k.P = p->num_proposals; k.C = p->num_classes; k.L = 5 + p->num_classes;
     uint32_t per = (k.P + kDecCluster - 1) / kDecCluster;
     k.rows_per_cta = (per + 31) & ~31u;
@@ -257,6 +264,10 @@ extern "C" tk_error_code_t tk_kernels_decode_detections(const tk_b200_decode_par
 
 tk_error_code_t tkb::decode_detections_packed(const tk_b200_decode_params_t* p, const float* d_objectness, cudaStream_t stream) {
     return decode_launch_common(p, d_objectness, nullptr, stream);
+}
+
+tk_error_code_t tkb::decode_detections_bitmap(const tk_b200_decode_params_t* p, const uint32_t* d_bitmap, cudaStream_t stream) {
+    return decode_launch_common(p, nullptr, nullptr, stream, d_bitmap);
 }
 
 // tk_kernels_postprocess_fused, layout 0: decode_kernel with the NMS tail.  `n` comes filled from post.cu

@@ -13,6 +13,8 @@ struct DecK {
     const float* logits;
     const float* obj;          // PACKED: dense objectness [frames][P] (the logits may then sit in host memory; only
                                // the surviving rows are read from them)
+    const uint32_t* bitmap;    // pass 1 done elsewhere (the pre-process kernel's scanner warps): [frames][nwf] ballot words
+    uint32_t nwf;              // bitmap words per frame = ceil(P / 32)
     tk_b200_candidate_t* cands;
     uint32_t* counts;
     uint32_t P, C, L;          // proposals, classes, row length 5+C

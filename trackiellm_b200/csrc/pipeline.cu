@@ -46,6 +46,8 @@ struct tk_b200_pipeline_s {
     cudaEvent_t ev_post, ev_fork, ev_join;
     int fused;                                         // fuse_postprocess: 0 / 1 separate kernels (default), 2 co-resident, 3 cluster-fused
     void* d_post_ws; size_t post_ws_bytes;             // its global NMS work area (frames above 512 candidates)
+    uint32_t* d_scan;                                  // [max_batch][ceil(P / 32)] ballot words of decode's pass 1, written by the pre-process kernel's scanner warps
+    int scan;                                          // 1: process_device runs that pass inside the pre-process kernel
     cudaEvent_t ev_uploaded[tkb::kSlots], ev_computed[tkb::kSlots], ev_downloaded[tkb::kSlots];
     uint8_t* d_frames[tkb::kSlots];                    // [chunk][frame_bytes (+ slack)]
     float*   d_logits[tkb::kSlots];                    // [chunk][P][5+C]
@@ -117,6 +119,7 @@ extern "C" void tk_b200_pipeline_destroy(tk_b200_pipeline_t** pp) {
         if (p->ev_fork) cudaEventDestroy(p->ev_fork);
         if (p->ev_join) cudaEventDestroy(p->ev_join);
         if (p->d_post_ws) cudaFree(p->d_post_ws);
+        if (p->d_scan) cudaFree(p->d_scan);
         cudaGetLastError();
     }
     delete p;
@@ -184,6 +187,14 @@ extern "C" tk_error_code_t tk_b200_pipeline_create(tk_b200_pipeline_t** out, con
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_dets), mb * p->cfg.max_detections * sizeof(tk_b200_candidate_t)) == cudaSuccess;
     ok = ok && cudaMalloc(reinterpret_cast<void**>(&p->d_ndets), mb * sizeof(uint32_t)) == cudaSuccess;
     ok = ok && cudaHostAlloc(reinterpret_cast<void**>(&p->h_cand_counts), mb * sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess;
+    // decode's pass 1 inside the pre-process kernel (preprocess.cu, ScanK): OFF unless TK_B200_SCAN=1.  Measured on
+    // 64 x 1080p (profiles/r2_experiments.md): decode_kernel 41.9 -> 18.2 us, but the scattered 64-byte fetches of the
+    // scan cost the pre-process kernel's row stream 27.5 us (119.2 -> 146.7 us) — the scan is DRAM work, not idle
+    // latency, and takes its ~23 us of the memory system wherever it runs; the step got 3.6 us slower.
+    p->scan = 0;
+    if (const char* e = getenv("TK_B200_SCAN")) p->scan = atoi(e) != 0;
+    if (ok && p->scan && cfg->num_proposals)
+        ok = cudaMalloc(reinterpret_cast<void**>(&p->d_scan), mb * ((cfg->num_proposals + 31) / 32) * sizeof(uint32_t)) == cudaSuccess;
     // decode + NMS as one kernel (post_mode); TK_B200_POST_FUSED overrides fuse_postprocess (experiments).
     p->fused = cfg->fuse_postprocess;
     if (const char* e = getenv("TK_B200_POST_FUSED")) p->fused = atoi(e);
@@ -292,7 +303,8 @@ static int post_mode(const tk_b200_pipeline_t* p, uint32_t n) {
 static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, const float* d_logits, uint32_t n,
                                    void* d_tensor, tk_b200_candidate_t* d_cands, uint32_t* d_counts,
                                    tk_b200_candidate_t* d_dets, uint32_t* d_ndets, cudaStream_t st,
-                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr, uint8_t* out_mode = nullptr) {
+                                   cudaEvent_t* tev = nullptr, const float* d_obj = nullptr, uint8_t* out_mode = nullptr,
+                                   bool pdl_pre = false) {
     const tk_b200_pipeline_config_t& c = p->cfg;
     tk_error_code_t rc;
     if (out_mode) *out_mode = 0;
@@ -335,9 +347,18 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
             mode = 0;                                          // a head shape its 25 KB do not hold: the two kernels, in stream
         }
     }
+    // decode's pass 1 rides in the pre-process kernel when both run in this call, back to back on one stream, on
+    // logits in HBM (the PACKED host path has its objectness column already)
+    const bool scan = p->scan && p->d_scan && d_frames && d_logits && !post_done && mode == 0 && !d_obj;
+    tk_b200_decode_params_t d{};
+    if (d_logits) {
+        d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
+        d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
+        d.d_candidates = d_cands; d.d_counts = d_counts; d.max_candidates = c.max_candidates;
+    }
     if (d_frames) {
         const tk_b200_preprocess_batch_params_t b = pre_params(p, d_frames, n, d_tensor);
-        if ((rc = tk_b200_preprocess_batch(&b, st)) != TK_SUCCESS) return rc;
+        if ((rc = preprocess_batch_impl(&b, st, pdl_pre, scan ? &d : nullptr, scan ? p->d_scan : nullptr)) != TK_SUCCESS) return rc;
     }
     if (tev) cudaEventRecord(tev[1], st);
     if (post_done) TK_CUDA_TRY(cudaStreamWaitEvent(st, p->ev_join, 0), TK_ERROR_GPU_CUDA_ERROR);
@@ -353,11 +374,7 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
         }
     }
     if (d_logits && !post_done) {
-        tk_b200_decode_params_t d{};
-        d.d_logits = d_logits; d.num_frames = n; d.num_proposals = c.num_proposals; d.num_classes = c.num_classes;
-        d.confidence_threshold = c.confidence_threshold; d.activation = c.activation;
-        d.d_candidates = d_cands; d.d_counts = d_counts; d.max_candidates = c.max_candidates;
-        if ((rc = decode_detections_packed(&d, d_obj, st)) != TK_SUCCESS) return rc;
+        if ((rc = scan ? decode_detections_bitmap(&d, p->d_scan, st) : decode_detections_packed(&d, d_obj, st)) != TK_SUCCESS) return rc;
         if (tev) cudaEventRecord(tev[2], st);
         tk_b200_nms_params_t m{};
         m.d_candidates = d_cands; m.d_counts = d_counts; m.num_frames = n; m.max_candidates = c.max_candidates;
@@ -394,7 +411,8 @@ extern "C" tk_error_code_t tk_b200_pipeline_process_device(tk_b200_pipeline_t* p
         mode = p->timing_mode + p->timing_calls;
         tev = p->timing_ev + 4 * (size_t)p->timing_calls++;
     }
-    return run_kernels(p, d_frames, d_logits, n, d_tensor, p->d_cands, p->d_counts, d_dets, d_ndets, stream, tev, nullptr, mode);
+    return run_kernels(p, d_frames, d_logits, n, d_tensor, p->d_cands, p->d_counts, d_dets, d_ndets, stream, tev, nullptr, mode,
+                       /*pdl_pre=*/true);
 }
 
 // Stage timing of process_device with CUDA events on the caller's stream.

@@ -26,11 +26,26 @@
 //   * EXACT arithmetic reproduces the reference's fp32 operation order with no
 //     contraction (bit-identical to its AVX build); the divide by std is the
 //     Markstein fma sequence on a host-computed correctly rounded reciprocal.
-#include "tk_common.cuh"
+#include "decode_row.cuh"
 
 namespace tkb {
 
 enum { FMT_RGB8 = 0, FMT_RGBA8 = 1, FMT_I420 = 2 };
+
+// Decode's pass 1 riding in this kernel (tk_b200_pipeline_process_device): one extra warp per CTA thresholds the
+// objectness word of a contiguous slice of the batch's logit rows (ld.global.nc.L2::64B, 8 loads in flight per lane)
+// and writes the warp-ballot words to `bitmap` ([frames][nwf] u32, bit b of word w of a frame = row 32 w + b passes),
+// which decode_kernel then loads instead of scanning.  That scan is the HBM half of decode — 1.6 M scattered 64-byte
+// fetches, 23 us of the 41 us decode_kernel takes behind this kernel — and it needs nothing this kernel's SMs are short
+// of: 64 more threads per SM, no shared memory, loads that wait on DRAM while the consumer warps issue arithmetic.
+struct ScanK {
+    const float* logits;      // nullptr: no scanner warp
+    uint32_t* bitmap;
+    uint32_t P, L, nwf;       // proposals per frame, row length, bitmap words per frame = ceil(P / 32)
+    uint32_t total_words;     // frames * nwf
+    float thr;
+    int act;                  // tk_b200_activation_e: RAW thresholds the word itself, the others its sigmoid
+};
 
 struct PreK {
     const uint8_t* in_base;
@@ -52,13 +67,14 @@ struct PreK {
     uint32_t tab_w;         // dst_w rounded up to 4
     uint32_t ring_off;      // byte offset of the ring in dynamic smem
     uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty row groups in flight
-    uint32_t big;           // 1: 512-thread CTAs (three row groups), 0: 352-thread CTAs (two)
+    uint32_t pdl;           // 1: launch as a programmatic dependent (pipeline only, see launch_variant)
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
     uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
     float one;              // 1.0f at run time (see sum2)
     unsigned long long cplane[3];   // byte offset of the tensor plane that SOURCE channel c is written to (BGR: 2 - c)
     TraceBuf trace;         // debug: per-CTA record (tk_b200_debug_trace), buf == nullptr when off
+    ScanK scan;
 };
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
@@ -283,10 +299,11 @@ __device__ __noinline__ void check_ring_row(const PreK& p, const uint8_t* base, 
 }
 #endif
 
-// BIG: 512-thread CTAs (three row groups of 160 consumer threads + the producer warp) at <= 64 registers instead of
-// 352-thread CTAs (two row groups) at <= 93: 32 resident warps per SM instead of 22.
-template <int FMT, bool F16, int AR, bool LBOX, bool TMA, bool BIG>
-__global__ void __launch_bounds__(BIG ? 512 : 352, 2) preprocess_kernel(const PreK p) {
+// Block: tx * ty consumer threads (320 at a 640-pixel row) + the producer warp (+ the scanner warp, see ScanK).
+// (512-thread CTAs — three row groups at <= 64 registers, 32 resident warps per SM instead of 22 — were built and
+// measured: 112.5 us against 112.0 us for 64 x 1080p EXACT -> fp16; the kernel is not short of warps.)
+template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
+__global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     // Output rows a warp takes per iteration.  2 was built and measured (the row set-up and the column constants are then
     // paid once per 8 pixels of a thread): 119.2 us against 112.1 us for 64 x 1080p EXACT -> fp16 — the longer release
     // interval of the ring costs more than the shorter instruction stream gains.  The loop below stays written for any RPI.
@@ -329,6 +346,34 @@ __global__ void __launch_bounds__(BIG ? 512 : 352, 2) preprocess_kernel(const Pr
     }
     __syncthreads();
 
+    // ======================= scanner warp (decode pass 1, see ScanK) =================
+    if (tid >= ncons + 32) {
+        const ScanK& s = p.scan;
+        const uint32_t lane = tid & 31;
+        const uint32_t w0 = (uint32_t)((unsigned long long)s.total_words * blockIdx.x / gridDim.x);
+        const uint32_t w1 = (uint32_t)((unsigned long long)s.total_words * (blockIdx.x + 1) / gridDim.x);
+        uint32_t frame = w0 / s.nwf, wi = w0 - frame * s.nwf;      // word w = frame * nwf + wi
+        for (uint32_t wb = w0; wb < w1; wb += 8) {
+            float obj[8];
+            uint32_t f = frame, i = wi;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t r = i * 32 + lane;
+                obj[u] = (wb + u < w1 && r < s.P) ? ld_obj(s.logits + ((size_t)f * s.P + r) * s.L + 4) : __int_as_float(0x7fc00000);
+                if (++i == s.nwf) { i = 0; ++f; }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float a = s.act == TK_B200_ACT_RAW ? obj[u] : tk_dm_sigmoidf(obj[u]);
+                const uint32_t b = __ballot_sync(0xffffffffu, a > s.thr);       // NaN never passes
+                if (lane == (uint32_t)u && wb + u < w1) s.bitmap[wb + u] = b;
+            }
+            frame = f; wi = i;
+        }
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        return;
+    }
+
     // This CTA's contiguous run of global output rows.
     const unsigned long long total = (unsigned long long)p.num_frames * p.dst_h;
     const unsigned long long g0 = total * blockIdx.x / gridDim.x;
@@ -347,7 +392,7 @@ __global__ void __launch_bounds__(BIG ? 512 : 352, 2) preprocess_kernel(const Pr
     };
 
     // ======================= producer warp =======================================
-    if (tid >= ncons) {
+    if (tid >= ncons) {                      // (the scanner warp, tid >= ncons + 32, left above)
         const uint32_t lane = tid - ncons;
         uint32_t seq = 0, min_rel = 0;       // every sequence below min_rel has been released by all consumer warps
         for (uint32_t f = f_first; f <= f_last; ++f) {
@@ -633,19 +678,21 @@ void letterbox_geometry(uint32_t sw, uint32_t sh, uint32_t dw, uint32_t dh,
 
 template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 static tk_error_code_t launch_variant(const PreK& k, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
-    auto kern = k.big ? preprocess_kernel<FMT, F16, AR, LBOX, TMA, true> : preprocess_kernel<FMT, F16, AR, LBOX, TMA, false>;
+    auto kern = preprocess_kernel<FMT, F16, AR, LBOX, TMA>;
     TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
     // Largest shared-memory carve-out, like post_kernel (post.cu), which the pipeline runs beside this kernel: with one
     // L1 / shared split for both, an SM never drains to reconfigure between them.
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    // Launched as a programmatic dependent (TK_B200_PDL_PRE=0 turns it off).  The kernel reads only the
-    // caller's frames, so behind a kernel that has announced (griddepcontrol.launch_dependents) that its
-    // dependents need not wait for it — nms_kernel of the previous step, which keeps 64 of 148 SMs busy at the
-    // bench batch — its CTAs take the idle SMs at once: 150.9 -> 147.6 us per 64-frame step, bit-exact.  Every
-    // thread ends on griddepcontrol.wait, so the grid completes after that kernel and stream order still holds
-    // for whatever follows.  Behind copies, events or kernels without the trigger nothing changes.
-    static const bool pdl = [] { const char* e = getenv("TK_B200_PDL_PRE"); return !e || atoi(e) != 0; }();
-    if (pdl) {
+    // k.pdl (set only by tk_b200_pipeline_process_device, never by the public launchers): launched as a programmatic
+    // dependent.  The kernel reads the caller's frames BEFORE its griddepcontrol.wait, so this is only sound behind a
+    // kernel that does not write them and has announced (griddepcontrol.launch_dependents) that its dependents need not
+    // wait for it — nms_kernel of the pipeline's previous step, which keeps 64 of 148 SMs busy at the bench batch: the
+    // pre-process CTAs take the idle SMs at once (150.9 -> 147.6 us per 64-frame step, bit-exact).  Every thread ends on
+    // griddepcontrol.wait, so the grid completes after that kernel and stream order still holds for whatever follows.
+    // Behind copies, events or kernels without the trigger (whatever the caller enqueued in between) nothing changes:
+    // those complete, memory and all, before this grid starts.  TK_B200_PDL_PRE=0 turns it off.
+    static const bool pdl_env = [] { const char* e = getenv("TK_B200_PDL_PRE"); return !e || atoi(e) != 0; }();
+    if (k.pdl && pdl_env) {
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
         cudaLaunchAttribute at[1];
@@ -705,6 +752,11 @@ bool tkb::preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t
 }
 
 extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_batch_params_t* prm, cudaStream_t stream) {
+    return tkb::preprocess_batch_impl(prm, stream, false, nullptr, nullptr);
+}
+
+tk_error_code_t tkb::preprocess_batch_impl(const tk_b200_preprocess_batch_params_t* prm, cudaStream_t stream, bool pdl_after_nms,
+                                           const tk_b200_decode_params_t* scan, uint32_t* d_scan_bitmap) {
     if (!prm || (!prm->d_input && !prm->d_input_ptrs) || !prm->d_output) return TK_ERROR_INVALID_ARGUMENT;
     if (prm->num_frames == 0) return TK_SUCCESS;
     if (prm->input_width == 0 || prm->input_height == 0 || prm->output_width == 0 || prm->output_height == 0)
@@ -750,6 +802,15 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     for (int c = 0; c < 3; ++c)
         k.cplane[c] = (unsigned long long)(bgr ? 2 - c : c) * k.dst_w * k.dst_h * (prm->output_type == TK_B200_OUT_F16 ? 2u : 4u);
     k.trace = trace_target();
+    k.pdl = pdl_after_nms ? 1u : 0u;
+    if (scan && d_scan_bitmap && scan->d_logits && scan->num_proposals) {
+        k.scan.logits = scan->d_logits; k.scan.bitmap = d_scan_bitmap;
+        k.scan.P = scan->num_proposals; k.scan.L = 5 + scan->num_classes; k.scan.nwf = (scan->num_proposals + 31) / 32;
+        const unsigned long long tw = (unsigned long long)scan->num_frames * k.scan.nwf;
+        if (tw > 0xffffffffull) return TK_ERROR_INVALID_DIMENSIONS;
+        k.scan.total_words = (uint32_t)tw;
+        k.scan.thr = scan->confidence_threshold; k.scan.act = (int)scan->activation;
+    }
     for (int c = 0; c < 3; ++c) {
         // constants are indexed by SOURCE channel; BGR byte c is tensor channel 2 - c
         const int tc = bgr ? 2 - c : c;
@@ -810,10 +871,7 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     // one more warp produces.
     const uint32_t Q = k.tab_w / 4;
     uint32_t tx = Q >= 160 ? 160 : ((Q + 31) & ~31u);
-    // TK_B200_PRE_BIG=1: 512-thread CTAs (A/B measurements; the default is what measured faster)
-    static const int big_env = [] { const char* e = getenv("TK_B200_PRE_BIG"); return e ? atoi(e) : 0; }();
-    k.big = (big_env == 1 && tx == 160) ? 1u : 0u;
-    uint32_t ty = (k.big ? 480 : 320) / tx; if (ty < 1) ty = 1;
+    uint32_t ty = 320 / tx; if (ty < 1) ty = 1;
 
     // Ring depth: the largest power of two (<= 32 slots) that fits the budget — two CTAs
     // per SM when that still covers the source rows `ty` consecutive output rows span plus
@@ -840,7 +898,7 @@ extern "C" tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_bat
     k.s_log2 = s_log2;
     k.tx = tx; k.ty = rows_in_flight;
     const size_t smem = k.ring_off + ((size_t)slot << s_log2);
-    dim3 block(tx * rows_in_flight + 32);
+    dim3 block(tx * rows_in_flight + 32 + (k.scan.logits ? 32 : 0));      // consumers + producer warp (+ scanner warp)
 
     const unsigned long long total_rows = (unsigned long long)k.num_frames * k.dst_h;
     const unsigned long long per_cta_min = 2ull * rows_in_flight;            // at least two rows per consumer stream

@@ -29,6 +29,13 @@ struct DeviceInfo {
 // Cached per-device properties; returns nullptr when no usable CUDA device.
 const DeviceInfo* device_info(int* out_device = nullptr);
 
+// preprocess.cu: tk_b200_preprocess_batch; pdl_after_nms = launch as a programmatic dependent (only the pipeline's
+// process_device passes true: there the kernel that precedes it on the stream is either its own nms_kernel or
+// something that completes before this grid starts).  scan + d_scan_bitmap: run decode's pass 1 in an extra warp of
+// every CTA (preprocess.cu, ScanK) and leave the ballot words in d_scan_bitmap [num_frames][ceil(P / 32)] for
+// decode_detections_bitmap.
+tk_error_code_t preprocess_batch_impl(const tk_b200_preprocess_batch_params_t* prm, cudaStream_t stream, bool pdl_after_nms,
+                                      const tk_b200_decode_params_t* scan, uint32_t* d_scan_bitmap);
 // preprocess.cu: see the definition.
 bool preprocess_reads_rows_sparsely(const tk_b200_preprocess_batch_params_t* prm);
 
@@ -49,6 +56,10 @@ tk_error_code_t postprocess_frame_uncapped(const float* d_logits, uint32_t P, ui
                                            float conf_thr, float iou_thr, uint32_t max_det, int class_agnostic,
                                            const uint32_t restore[4], tk_b200_candidate_t* d_dets, uint32_t* d_ndets,
                                            cudaStream_t st);
+
+// decode.cu: decode_kernel with pass 1 already done — d_bitmap [frames][ceil(P / 32)] as the pre-process kernel's
+// scanner warps leave it.
+tk_error_code_t decode_detections_bitmap(const tk_b200_decode_params_t* p, const uint32_t* d_bitmap, cudaStream_t stream);
 
 // Number of kernels this library has enqueued (every launcher goes through
 // launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
