@@ -76,6 +76,21 @@ def test_reference_softmax_test_program():
     assert r.returncode == 0, r.stdout + r.stderr
 
 
+def test_reference_attribute_test_program():
+    """The reference's own tests/tk_attribute_classifier_test.c, unmodified, linked against libtk_b200.so must behave
+    exactly as it does linked against the reference's own code (tests/test_oracle.py::
+    test_reference_attribute_program_on_the_reference_itself): red KAT OK, door KAT aborting on the same assertion —
+    the reference's door test fails on the reference; a drop-in reproduces that, it does not "fix" it."""
+    from test_oracle import run_reference_attribute_program
+    exe = os.path.join(ROOT, "oracle", "_ref", "tk_attribute_classifier_test")
+    ref = os.path.join(ROOT, "oracle", "_ref", "tk_attribute_classifier_test_ref")
+    if not (os.path.exists(exe) and os.path.exists(ref)):
+        pytest.skip("oracle/_ref test programs not built")
+    got, want = run_reference_attribute_program(exe), run_reference_attribute_program(ref)
+    assert got == want, (got, want)
+    assert "test_classify_red_color... OK" in got[1] and got[0] != 0
+
+
 def test_dominant_color_golden_and_oracle():
     fr = G["color_frame"]
     ids, bins = V.dominant_color(torch.from_numpy(fr).cuda(), torch.from_numpy(G["color_boxes"]).cuda(), want_bins=True)

@@ -263,3 +263,26 @@ def test_detection_distance_reference_kat():
     for t in f:
         acc = np.float32(acc + t)
     assert O.detection_distance((8, 6, 70, 60), dm, 120, 100) == float(np.float32(acc / np.float32(len(f))))
+
+
+def run_reference_attribute_program(exe):
+    """(return code, stdout, assertion text without the program name) of the reference's tk_attribute_classifier_test."""
+    import subprocess
+    r = subprocess.run(["stdbuf", "-o0", exe], capture_output=True, text=True)
+    err = r.stderr.strip().split(": ", 1)[-1] if r.stderr.strip() else ""
+    return r.returncode, r.stdout, err
+
+
+def test_reference_attribute_program_on_the_reference_itself():
+    """The reference's own test program (tests/tk_attribute_classifier_test.c, unmodified) linked against the reference's
+    own tk_attribute_classifier.c (oracle/_ref/libtkref.so): its red KAT passes; its door KAT ABORTS — the code
+    compares the rows above and below a pixel (tk_attribute_classifier.c:127-135) and the KAT draws vertical bars, so
+    the reference answers "open" where its test expects "closed".  This transcript is the yardstick the GPU build of the
+    same program must reproduce (tests/test_gpu_rows_attrs.py::test_reference_attribute_test_program)."""
+    exe = os.path.join(os.path.dirname(O.__file__), "_ref", "tk_attribute_classifier_test_ref")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rc, out, err = run_reference_attribute_program(exe)
+    assert "test_classify_red_color... OK" in out
+    assert "test_classify_door_closed" in out and "All Attribute Classifier Tests Passed" not in out
+    assert rc != 0 and 'strcmp(state_name, "closed") == 0' in err

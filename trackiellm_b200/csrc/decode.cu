@@ -26,6 +26,7 @@
 #include "decode_row.cuh"
 #include "nms_frame.cuh"
 
+#include <stdlib.h>
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -146,6 +147,9 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
             sp[4] = (uint32_t)c.bbox.h; sp[5] = __float_as_uint(c.confidence); sp[6] = c.class_id;
         }
     };
+    // (Fetching all of a CTA's ~60 surviving rows into shared memory at once with cp.async — one DRAM round trip instead
+    // of ~4 dependent ones per warp — was built and measured: 36.2 us against 35.0 us for 64 frames.  The pass is not a
+    // latency chain: with 64 warps per SM in it, other warps' rows are in flight while one waits.)
     for (uint32_t sidx = warp; sidx < lim; sidx += kDecWarps) {
         const uint32_t r = row_of(sidx);
         RowRegs q;

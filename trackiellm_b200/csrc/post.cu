@@ -41,13 +41,6 @@ struct PostK {
     TraceBuf trace;          // debug: per-frame record (tk_b200_debug_trace)
 };
 
-__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 template <int ACT, bool PACKED>
 __global__ void __launch_bounds__(kPostThreads, 8) post_kernel(const PostK k) {
     extern __shared__ __align__(16) uint8_t dsm[];
