@@ -104,8 +104,10 @@ typedef enum { TK_B200_RESIZE_STRETCH = 0, TK_B200_RESIZE_LETTERBOX = 1 } tk_b20
  *        bit-identical to the reference's AVX build.
  * FAST : lerp form with FMA; within 1e-5 + 1e-5|ref| of the reference.
  * HALF : fp16 output only (RGB8 / RGBA8 input; otherwise FAST is used): bytes
- *        become exact half2 pairs and the lerps run in HFMA2; within the
- *        1e-2 + 1e-2|ref| fp16 bar of the reference (measured max ~4e-3). */
+ *        become exact half2 pairs centred on 128 and the lerps run in HFMA2;
+ *        within HALF of the 1e-2 + 1e-2|ref| fp16 bar of the reference for any
+ *        content (bound derived in DESIGN.md §3, asserted on adversarial frames).
+ * EXACT is what every handle and launcher uses unless told otherwise. */
 typedef enum { TK_B200_ARITH_EXACT = 0, TK_B200_ARITH_FAST = 1, TK_B200_ARITH_HALF = 2 } tk_b200_arith_e;
 typedef enum { TK_B200_ACT_RAW = 0, TK_B200_ACT_SIGMOID = 1, TK_B200_ACT_SOFTMAX = 2 } tk_b200_activation_e;
 

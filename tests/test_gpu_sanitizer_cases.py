@@ -1,8 +1,11 @@
 """Small GPU cases that reach every kernel template variant once, each checked against the oracle.
 
-Two uses: (1) part of the ordinary `-m gpu` suite; (2) the selection `tools/run_sanitizer.sh` runs under
-`compute-sanitizer --tool memcheck | racecheck | synccheck | initcheck` — the inputs are kept small
-so that the 10-1000x slow-down of the tools still ends in minutes.  Variants covered:
+Three uses: (1) part of the ordinary `-m gpu` suite; (2) the core of what `tools/run_checked.sh` runs against the
+CHECKED build of the library (device-side assertions + ring-content verification, csrc/tk_common.cuh) — the stand-in
+for compute-sanitizer, which is closed on this GPU pool (profiles/r2_sanitizer.md); (3) the selection
+`tools/run_sanitizer.sh` runs under `compute-sanitizer --tool memcheck | racecheck | synccheck | initcheck`
+where that tool is open — the inputs are kept small so that its 10-1000x slow-down still ends in minutes.
+Variants covered:
 
   pre-process : TMA and cooperative-copy staging, dense and sparse row staging, RGB8 / BGR8 / RGBA8 / I420,
                 stretch and letterbox, EXACT / FAST / HALF arithmetic, fp32 and fp16 tensors, several CTAs per frame
