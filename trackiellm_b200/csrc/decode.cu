@@ -47,6 +47,10 @@ struct NmsTail {
 // co-resident (a cluster of 8 must sit in one GPC) and the launch needs two waves.
 template <int ACT, bool PACKED, bool NMS>
 __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, const NmsTail tail) {
+    // Possibly launched under the tail of the pipeline's pre-process kernel (pdl_chain_hint): nothing is read or written
+    // before that grid has completed.  A no-op for a plain launch.  Then let nms_kernel, which starts the same way, in.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     extern __shared__ __align__(16) uint8_t dsm[];
     uint32_t* flags = reinterpret_cast<uint32_t*>(dsm);            // [nwords] ballot bitmap
     uint32_t* wpre = flags + k.nwords;                             // [nwords] exclusive prefix of popc
@@ -220,10 +224,12 @@ static tk_error_code_t launch_decode(const DecK& k, const NmsTail* tail, uint32_
     cfg.blockDim = dim3(kDecThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = kDecCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_chain_hint() ? 2 : 1;
     TK_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, k, t), TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE);
     return launch_status(tail ? "decode_kernel+nms" : "decode_kernel");
 }

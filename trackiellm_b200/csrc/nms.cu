@@ -38,6 +38,7 @@ namespace tkb {
 __global__ void __launch_bounds__(kNmsThreads, 3) nms_kernel(const NmsK k) {
     // Nothing this grid reads is written by the kernel the pipeline launches next (the pre-process kernel of the
     // following step, which ends on griddepcontrol.wait): let it start on the SMs this grid does not fill.
+    asm volatile("griddepcontrol.wait;" ::: "memory");            // (launched under decode_kernel's tail by the pipeline; else a no-op)
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     extern __shared__ __align__(16) uint8_t dsm[];
     for (uint32_t frame = blockIdx.x; frame < k.num_frames; frame += gridDim.x) {
@@ -108,7 +109,18 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
             cudaGetLastError(); per_sm = 1;
         }
         const uint32_t cap = sms * (uint32_t)per_sm;
-        nms_kernel<<<p->num_frames < cap ? p->num_frames : cap, kNmsThreads, smem, stream>>>(k);
+        if (pdl_chain_hint()) {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(p->num_frames < cap ? p->num_frames : cap); cfg.blockDim = dim3(kNmsThreads);
+            cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            TK_CUDA_TRY(cudaLaunchKernelEx(&cfg, nms_kernel, k), TK_ERROR_CUDA_KERNEL_LAUNCH_FAILURE);
+        } else {
+            nms_kernel<<<p->num_frames < cap ? p->num_frames : cap, kNmsThreads, smem, stream>>>(k);
+        }
         return launch_status("nms_kernel");
     }
     // More frames than SMs: shared memory sized for the cap (200 KB at 4096 candidates) means one CTA per SM and

@@ -68,6 +68,7 @@ struct PreK {
     uint32_t ring_off;      // byte offset of the ring in dynamic smem
     uint32_t tx, ty;        // consumer threads: tx along the row (multiple of 32), ty row groups in flight
     uint32_t pdl;           // 1: launch as a programmatic dependent (pipeline only, see launch_variant)
+    uint32_t trigger;       // 1: the pipeline's decode_kernel follows on the stream and may be launched under this grid's tail
     uint32_t vec_store;     // 1: dst_w % 4 == 0 and the output base is 16-byte aligned
     uint32_t sparse;        // 1: y_ratio >= 2 — only the two source rows of each output row are staged
     uint32_t swap_rb;       // 1: BGR byte order — source channel c lands in tensor plane 2 - c
@@ -323,6 +324,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     const uint32_t S = 1u << p.s_log2, smask = S - 1;
     unsigned long long t_trace[2];
     if (p.trace.buf && tid == 0) t_trace[0] = gtimer();
+    if (p.trigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // decode_kernel starts on griddepcontrol.wait
 
     if (tid == 0) {
         for (uint32_t s = 0; s < S; ++s) mbar_init(&full[s], 1);
@@ -399,23 +401,27 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
             uint32_t h0, h1, a; item_rows(f, h0, h1);
             int ylo, n; item_src_rows(p, h0, h1, ylo, n, a);
             const uint8_t* base = frame_ptr(f);
-            for (int r = 0; r < n; ++r, ++seq) {
-                const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
-                const uint32_t slot = seq & smask;
-                if (seq >= S) {
-                    while (seq - S >= min_rel) {                   // slot still holds a row somebody may read
-                        min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
-                        if (seq - S >= min_rel) __nanosleep(100);
-                    }
-                    __threadfence_block();
-                    // every staged row is waited on by the warps that sample it before they move
-                    // past it, so the slot's previous copy has landed; the check is free then.
-                    if (TMA && lane == 0) mbar_wait(&full[slot], ((seq >> p.s_log2) - 1u) & 1u);
-                }
-                uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
-                const uint8_t* src = base + (size_t)row * p.src_stride;
-                if constexpr (TMA) {
-                    if (lane == 0) {
+            if constexpr (TMA) {
+                // Rows are armed in BATCHES, one lane per row: every sequence number below min_rel + S has a free slot, so
+                // up to 32 of them get their source address, their slot's previous-phase check, their expect_tx and their
+                // bulk copy in one pass of the warp.  (One row per loop trip — ~95 dependent instructions each, two CTA
+                // fences among them — made this single warp the kernel's pacemaker: ncu showed it busy throughout, the
+                // slot it wanted already free 78 % of the time, and 20 % of the consumers' samples on the `full` barriers.)
+                for (int r0 = 0; r0 < n;) {
+                    min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
+                    const uint32_t room = min_rel + S - seq;          // sequences seq .. seq + room - 1 may be armed now
+                    if (room == 0) { __nanosleep(100); continue; }
+                    const uint32_t k = min(min(room, 32u), (uint32_t)(n - r0));
+                    __threadfence_block();                            // the releases read above happen-before the overwrites below
+                    if (lane < k) {
+                        const int r = r0 + (int)lane;
+                        const uint32_t q = seq + lane, slot = q & smask;
+                        const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
+                        // every staged row is waited on by the warps that sample it before they move past it, so the
+                        // slot's previous copy has landed; the check is free then.
+                        if (q >= S) mbar_wait(&full[slot], ((q >> p.s_log2) - 1u) & 1u);
+                        uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
+                        const uint8_t* src = base + (size_t)row * p.src_stride;
                         fence_proxy_async();
                         if constexpr (FMT == FMT_I420) {
                             const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
@@ -428,7 +434,25 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
                             bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
                         }
                     }
-                } else {
+                    __syncwarp();
+                    // A waiter tells phases apart by parity only, so it may look at full[slot] for sequence q only once
+                    // q has been armed (which implies q - S has completed): publish after every lane has armed its row.
+                    if (lane == 0) { __threadfence_block(); *staged = seq + k; }
+                    seq += k; r0 += (int)k;
+                }
+            } else {
+                for (int r = 0; r < n; ++r, ++seq) {
+                    const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
+                    const uint32_t slot = seq & smask;
+                    if (seq >= S) {
+                        while (seq - S >= min_rel) {                   // slot still holds a row somebody may read
+                            min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
+                            if (seq - S >= min_rel) __nanosleep(100);
+                        }
+                        __threadfence_block();
+                    }
+                    uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
+                    const uint8_t* src = base + (size_t)row * p.src_stride;
                     const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
                     warp_copy_unaligned(dst, src, nb, lane);
                     if constexpr (FMT == FMT_I420) {
@@ -437,11 +461,8 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
                         warp_copy_unaligned(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
                     }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&full[slot]);
+                    if (lane == 0) { mbar_arrive(&full[slot]); __threadfence_block(); *staged = seq + 1; }
                 }
-                // A waiter tells phases apart by parity only, so it may look at full[slot] for
-                // sequence q only once q has been armed (which implies q - S has completed).
-                if (lane == 0) { __threadfence_block(); *staged = seq + 1; }
             }
         }
         asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -803,6 +824,7 @@ tk_error_code_t tkb::preprocess_batch_impl(const tk_b200_preprocess_batch_params
         k.cplane[c] = (unsigned long long)(bgr ? 2 - c : c) * k.dst_w * k.dst_h * (prm->output_type == TK_B200_OUT_F16 ? 2u : 4u);
     k.trace = trace_target();
     k.pdl = pdl_after_nms ? 1u : 0u;
+    k.trigger = pdl_chain_hint() ? 1u : 0u;
     if (scan && d_scan_bitmap && scan->d_logits && scan->num_proposals) {
         k.scan.logits = scan->d_logits; k.scan.bitmap = d_scan_bitmap;
         k.scan.P = scan->num_proposals; k.scan.L = 5 + scan->num_classes; k.scan.nwf = (scan->num_proposals + 31) / 32;

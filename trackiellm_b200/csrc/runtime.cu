@@ -17,6 +17,8 @@ static std::atomic<unsigned long long*> g_trace_buf{nullptr};
 static std::atomic<uint32_t> g_trace_cap{0};
 TraceBuf trace_target() { return TraceBuf{g_trace_buf.load(std::memory_order_relaxed), g_trace_cap.load(std::memory_order_relaxed)}; }
 
+bool& pdl_chain_hint() { static thread_local bool on = false; return on; }
+
 static DeviceInfo g_info[64];
 static int g_info_state[64];   // 0 unknown, 1 ok, -1 bad
 static std::mutex g_info_mu;

@@ -61,6 +61,15 @@ tk_error_code_t postprocess_frame_uncapped(const float* d_logits, uint32_t P, ui
 // scanner warps leave it.
 tk_error_code_t decode_detections_bitmap(const tk_b200_decode_params_t* p, const uint32_t* d_bitmap, cudaStream_t stream);
 
+// Programmatic-dependent-launch chain of one pipeline step (pre-process -> decode -> NMS on one stream).  The pipeline's
+// process_device sets this thread-local hint around its three launches: the pre-process kernel then announces its
+// dependents at its top, and decode_kernel / nms_kernel are launched with the programmatic-serialization attribute.  Both
+// start with griddepcontrol.wait as their FIRST instruction, so the full data dependency is kept (nothing is read or
+// written before the predecessor grid has completed and flushed): only launch latency, CTA scheduling and the kernel
+// prologue move under the predecessor's tail.  Measured slower (see pipeline.cu) and therefore opt-in
+// (TK_B200_PDL_CHAIN=1); off (plain launches) for every other caller in any case.
+bool& pdl_chain_hint();
+
 // Number of kernels this library has enqueued (every launcher goes through
 // launch_status); read by tk_b200_launch_count() for bench.py's gpu_launches.
 void count_launch();
