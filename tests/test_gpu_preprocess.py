@@ -280,3 +280,38 @@ def test_random_geometries_all_formats_bitexact():
         for i in range(n):
             ref = O.preprocess_rgb8(rgb[i], ow, oh)
             assert np.array_equal(bits(got[i]), bits(ref)), (case, fmt, w, h, ow, oh, n, stride, i)
+
+
+def test_host_entry_point_threads_do_not_leak_device_memory():
+    """The host-pointer entry points keep a stream and grow-only device buffers per calling thread (they were
+    never released).  30 short-lived threads, each one 1080p call: the device's free memory after they are gone is what
+    it was before them (within one allocator granule), and tk_b200_thread_release() frees the caller's own."""
+    import threading
+    from trackiellm_b200 import _capi as capi
+    fr = synth.rgb_frame(1920, 1080, 1)
+    ref = O.preprocess_rgb8(fr, 640, 640)
+    V.preprocessor_resize_and_normalize_to_chw(fr, 640, 640)          # this thread's scratch exists from here on
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    errs = []
+
+    def work():
+        try:
+            got = V.preprocessor_resize_and_normalize_to_chw(fr, 640, 640)
+            if not np.array_equal(bits(got), bits(ref)):
+                errs.append("mismatch")
+        except Exception as e:      # noqa: BLE001
+            errs.append(repr(e))
+
+    for _ in range(30):
+        t = threading.Thread(target=work)
+        t.start(); t.join()
+    assert not errs, errs
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 < 4 << 20, (free0, free1)       # 30 leaked scratches would be ~330 MB
+    capi.lib().tk_b200_thread_release()
+    torch.cuda.synchronize()
+    free2, _ = torch.cuda.mem_get_info()
+    assert free2 >= free1 + (8 << 20)                     # this thread's ~11 MB of scratch went back
+    assert np.array_equal(bits(V.preprocessor_resize_and_normalize_to_chw(fr, 640, 640)), bits(ref))   # and it comes back on demand
