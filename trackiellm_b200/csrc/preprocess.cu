@@ -308,7 +308,11 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     // Output rows a warp takes per iteration.  2 was built and measured (the row set-up and the column constants are then
     // paid once per 8 pixels of a thread): 119.2 us against 112.1 us for 64 x 1080p EXACT -> fp16 — the longer release
     // interval of the ring costs more than the shorter instruction stream gains.  The loop below stays written for any RPI.
+#ifdef TK_PRE_RPI
+    constexpr int RPI = TK_PRE_RPI;      // experiment builds only (1080p -> 640: the 16-slot ring covers 4 rows in flight)
+#else
     constexpr int RPI = 1;
+#endif
     constexpr bool EXACT = (AR == AR_EXACT);
     static_assert(AR != AR_HALF || (F16 && FMT != FMT_I420), "HALF arithmetic: fp16 output, RGB8/RGBA8 input");
     extern __shared__ __align__(128) uint8_t smem[];
