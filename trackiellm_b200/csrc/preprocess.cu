@@ -300,27 +300,41 @@ __device__ __noinline__ void check_ring_row(const PreK& p, const uint8_t* base, 
 }
 #endif
 
+// Row records: everything a consumer warp needs to know about one output row, worked out ONCE by the producer warp
+// (one lane per row, up to 32 rows per pass) instead of by each of the row's five consumer warps — source-row index,
+// y weight, ring slots, barrier parities, output address.  ~95 instructions of per-row set-up in every consumer warp
+// become two 16-byte shared-memory loads (profiles/r2_experiments.md §9: the EXACT kernel is bound by the instructions
+// it issues, ALU-pipe ones first).
+//   word 0, 1  byte offsets (from the start of dynamic shared memory) of the ring slots holding source rows y, y + 1
+//   word 2     y weight (fp32 bits)
+//   word 3     bit 0: the row lies inside the resized region (else it is letterbox padding: no source rows);
+//              bit 1, 2: phase parities of the two slots' `full` barriers for these rows
+//   word 4, 5  shared-window addresses of those two barriers
+//   word 6, 7  address of the output row in tensor plane 0 of its frame
+// Record n (the CTA's n-th output row) lives in entry n mod kRecs and is published through `rec_ready` once both its
+// source rows have been armed; entry n is reused for row n + kRecs only when every consumer warp has moved past row n.
+static constexpr uint32_t kRecs = 32;
+static constexpr uint32_t kSmemRecs = 512;                        // 32 x 32 B
+static constexpr uint32_t kSmemQ0 = kSmemRecs + kRecs * 32;       // [kRecs] u32: first ring sequence number row n needs (producer only)
+static constexpr uint32_t kSmemChk = kSmemQ0 + kRecs * 4;         // CHECKED build: [kRecs] {frame, source row, n}
+static constexpr uint32_t kSmemTabs = 2048;                       // column tables
+
 // Block: tx * ty consumer threads (320 at a 640-pixel row) + the producer warp (+ the scanner warp, see ScanK).
 // (512-thread CTAs — three row groups at <= 64 registers, 32 resident warps per SM instead of 22 — were built and
-// measured: 112.5 us against 112.0 us for 64 x 1080p EXACT -> fp16; the kernel is not short of warps.)
+// measured: 112.5 us against 112.0 us for 64 x 1080p EXACT -> fp16; the kernel is not short of warps.  Two output rows
+// per warp iteration: 117.3 us against 111.1 us — the set-up it meant to share is per row, see the records above.)
 template <int FMT, bool F16, int AR, bool LBOX, bool TMA>
 __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
-    // Output rows a warp takes per iteration.  2 was built and measured (the row set-up and the column constants are then
-    // paid once per 8 pixels of a thread): 119.2 us against 112.1 us for 64 x 1080p EXACT -> fp16 — the longer release
-    // interval of the ring costs more than the shorter instruction stream gains.  The loop below stays written for any RPI.
-#ifdef TK_PRE_RPI
-    constexpr int RPI = TK_PRE_RPI;      // experiment builds only (1080p -> 640: the 16-slot ring covers 4 rows in flight)
-#else
-    constexpr int RPI = 1;
-#endif
     constexpr bool EXACT = (AR == AR_EXACT);
     static_assert(AR != AR_HALF || (F16 && FMT != FMT_I420), "HALF arithmetic: fp16 output, RGB8/RGBA8 input");
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);                 // 32 x 8 B
-    volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(full + 32);   // one per consumer warp (<= 32)
-    volatile uint32_t* staged = progress + 32;   // number of sequence numbers the producer has armed so far
-    int* xb_tab = reinterpret_cast<int*>(smem + 512);
-    float* xd_tab = reinterpret_cast<float*>(smem + 512 + 4 * p.tab_w);
+    volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(full + 32);   // per consumer warp (<= 32): the row it is on
+    volatile uint32_t* rec_ready = progress + 32;                       // number of row records published so far
+    uint4* recs = reinterpret_cast<uint4*>(smem + kSmemRecs);
+    volatile uint32_t* q0s = reinterpret_cast<volatile uint32_t*>(smem + kSmemQ0);
+    int* xb_tab = reinterpret_cast<int*>(smem + kSmemTabs);
+    float* xd_tab = reinterpret_cast<float*>(smem + kSmemTabs + 4 * p.tab_w);
     uint8_t* ring = smem + p.ring_off;
 
     const uint32_t tid = threadIdx.x;
@@ -335,7 +349,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         mbar_fence_init();
     }
     if (tid < 32) progress[tid] = tid < (ncons >> 5) ? 0u : 0xffffffffu;
-    if (tid == 0) *staged = 0u;
+    if (tid == 0) *rec_ready = 0u;
     // Column table: byte offset of the left source pixel and x weight
     // (src/vision/tk_image_preprocessor.c:48,50,52).
     for (uint32_t w = tid; w < p.tab_w; w += blockDim.x) {
@@ -385,102 +399,162 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     const unsigned long long g0 = total * blockIdx.x / gridDim.x;
     const unsigned long long g1 = total * (blockIdx.x + 1) / gridDim.x;
     if (g0 >= g1) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
-    const uint32_t f_first = (uint32_t)(g0 / p.dst_h);
-    const uint32_t f_last = (uint32_t)((g1 - 1) / p.dst_h);
-
-    auto item_rows = [&](uint32_t f, uint32_t& h0, uint32_t& h1) {
-        h0 = (f == f_first) ? (uint32_t)(g0 - (unsigned long long)f_first * p.dst_h) : 0u;
-        unsigned long long end = g1 - (unsigned long long)f * p.dst_h;
-        h1 = end < p.dst_h ? (uint32_t)end : p.dst_h;
-    };
-    auto frame_ptr = [&](uint32_t f) -> const uint8_t* {
-        return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
-    };
+    const uint32_t nrows_cta = (uint32_t)(g1 - g0);
+    constexpr uint32_t ESZ = F16 ? 2 : 4;
 
     // ======================= producer warp =======================================
+    // Two cursors over the CTA's items (an item = the CTA's rows inside one frame): the ARMING cursor walks the source-row
+    // sequence and issues the copies as slots free up; the RECORD cursor walks the output rows and publishes a row's
+    // record once both its source rows are armed.  Consumers report the ROW they are on; the ring sequence number that
+    // releases is looked up here (q0s), so sequence arithmetic lives in this warp only.
     if (tid >= ncons) {                      // (the scanner warp, tid >= ncons + 32, left above)
         const uint32_t lane = tid - ncons;
-        uint32_t seq = 0, min_rel = 0;       // every sequence below min_rel has been released by all consumer warps
-        for (uint32_t f = f_first; f <= f_last; ++f) {
-            uint32_t h0, h1, a; item_rows(f, h0, h1);
-            int ylo, n; item_src_rows(p, h0, h1, ylo, n, a);
-            const uint8_t* base = frame_ptr(f);
-            if constexpr (TMA) {
-                // Rows are armed in BATCHES, one lane per row: every sequence number below min_rel + S has a free slot, so
-                // up to 32 of them get their source address, their slot's previous-phase check, their expect_tx and their
-                // bulk copy in one pass of the warp.  (One row per loop trip — ~95 dependent instructions each, two CTA
-                // fences among them — made this single warp the kernel's pacemaker: ncu showed it busy throughout, the
-                // slot it wanted already free 78 % of the time, and 20 % of the consumers' samples on the `full` barriers.)
-                for (int r0 = 0; r0 < n;) {
-                    min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
-                    const uint32_t room = min_rel + S - seq;          // sequences seq .. seq + room - 1 may be armed now
-                    if (room == 0) { __nanosleep(100); continue; }
-                    const uint32_t k = min(min(room, 32u), (uint32_t)(n - r0));
-                    __threadfence_block();                            // the releases read above happen-before the overwrites below
-                    if (lane < k) {
-                        const int r = r0 + (int)lane;
-                        const uint32_t q = seq + lane, slot = q & smask;
-                        const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
-                        // every staged row is waited on by the warps that sample it before they move past it, so the
-                        // slot's previous copy has landed; the check is free then.
-                        if (q >= S) mbar_wait(&full[slot], ((q >> p.s_log2) - 1u) & 1u);
+        const uint32_t f_first = (uint32_t)(g0 / p.dst_h), f_last = (uint32_t)((g1 - 1) / p.dst_h);
+        auto item_rows = [&](uint32_t f, uint32_t& h0, uint32_t& h1) {
+            h0 = (f == f_first) ? (uint32_t)(g0 - (unsigned long long)f_first * p.dst_h) : 0u;
+            unsigned long long end = g1 - (unsigned long long)f * p.dst_h;
+            h1 = end < p.dst_h ? (uint32_t)end : p.dst_h;
+        };
+        auto frame_ptr = [&](uint32_t f) -> const uint8_t* {
+            return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
+        };
+        const size_t plane = (size_t)p.dst_w * p.dst_h;
+        uint32_t fa = f_first, seq = 0, a_a = 0;                 // arming cursor: frame, sequences armed so far, first inside row
+        int ra = 0, na = 0, ylo_a = 0;                           //   rows armed / to arm in the item, its first source row
+        const uint8_t* base_a = nullptr;
+        bool a_open = false, a_done = false;
+        uint32_t fr = f_first, hr = 0, h1r = 0, a_r = 0, b_r = 0, seqbase_r = 0, n_pub = 0;   // record cursor
+        int ylo_r = 0, nrows_r = 0;
+        bool r_open = false;
+#ifdef TK_B200_CHECKED
+        volatile uint32_t* chk = reinterpret_cast<volatile uint32_t*>(smem + kSmemChk);
+#endif
+        while (n_pub < nrows_cta) {                              // the last record needs the last source row: arming ends first
+            if (!a_open && !a_done) {
+                uint32_t h0, h1; item_rows(fa, h0, h1);
+                item_src_rows(p, h0, h1, ylo_a, na, a_a);
+                base_a = frame_ptr(fa); ra = 0; a_open = true;
+            }
+            if (!r_open) {
+                uint32_t h0, h1; item_rows(fr, h0, h1);
+                item_src_rows(p, h0, h1, ylo_r, nrows_r, a_r);
+                hr = h0; h1r = h1; b_r = min(h1, p.pad_top + p.new_h); r_open = true;
+            }
+            // lane j looks at output row hr + j of the record cursor's item
+            const uint32_t h = hr + lane;
+            const bool in_item = h < h1r;
+            const bool inside = in_item && h >= a_r && h < b_r;
+            int y = 0; float yd = 0.0f;
+            uint32_t q0 = seqbase_r + (h >= b_r ? (uint32_t)nrows_r : 0u);   // padding: above the region nothing is released yet, below it everything
+            if (inside) {
+                const float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));    // src/vision/tk_image_preprocessor.c:49,51,53
+                y = min(__float2int_rz(gy), (int)p.src_h - 2);
+                yd = __fsub_rn(gy, (float)y);
+                q0 = seqbase_r + (p.sparse ? 2u * (h - a_r) : (uint32_t)(y - ylo_r));
+            }
+            // every sequence below min_rel has been released by all consumer warps
+            const uint32_t min_n = __reduce_min_sync(0xffffffffu, progress[lane]);
+            const uint32_t q0_next = __shfl_sync(0xffffffffu, q0, 0);
+            const uint32_t min_rel = min_n < n_pub ? q0s[min_n & (kRecs - 1)] : q0_next;
+            bool did = false;
+            if (a_open) {
+                const uint32_t room = min_rel + S - seq;          // sequences seq .. seq + room - 1 may be armed now
+                if constexpr (TMA) {
+                    // Rows are armed in BATCHES, one lane per row.  (One row per loop trip — ~95 dependent instructions each,
+                    // two CTA fences among them — made this single warp the kernel's pacemaker: ncu showed it busy throughout,
+                    // the slot it wanted already free 78 % of the time, 20 % of the consumers' samples on the `full` barriers.)
+                    const uint32_t k = min(min(room, 32u), (uint32_t)(na - ra));
+                    if (k) {
+                        __threadfence_block();                    // the releases read above happen-before the overwrites below
+                        if (lane < k) {
+                            const int r = ra + (int)lane;
+                            const uint32_t q = seq + lane, slot = q & smask;
+                            const int row = p.sparse ? src_row_of(p, a_a + ((uint32_t)r >> 1)) + (r & 1) : ylo_a + r;
+                            // every staged row is waited on by the warps that sample it before they move past it, so the
+                            // slot's previous copy has landed; the check is free then.
+                            if (q >= S) mbar_wait(&full[slot], ((q >> p.s_log2) - 1u) & 1u);
+                            uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
+                            const uint8_t* src = base_a + (size_t)row * p.src_stride;
+                            fence_proxy_async();
+                            if constexpr (FMT == FMT_I420) {
+                                const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
+                                mbar_arrive_expect_tx(&full[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
+                                bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
+                                bulk_g2s(dst + p.u_slot_off, base_a + p.u_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
+                                bulk_g2s(dst + p.v_slot_off, base_a + p.v_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
+                            } else {
+                                mbar_arrive_expect_tx(&full[slot], p.copy_bytes);
+                                bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
+                            }
+                        }
+                        __syncwarp();
+                        seq += k; ra += (int)k; did = true;
+                    }
+                } else {
+                    if (room && ra < na) {
+                        __threadfence_block();
+                        const int row = p.sparse ? src_row_of(p, a_a + ((uint32_t)ra >> 1)) + (ra & 1) : ylo_a + ra;
+                        const uint32_t slot = seq & smask;
                         uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
-                        const uint8_t* src = base + (size_t)row * p.src_stride;
-                        fence_proxy_async();
+                        const uint8_t* src = base_a + (size_t)row * p.src_stride;
+                        const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
+                        warp_copy_unaligned(dst, src, nb, lane);
                         if constexpr (FMT == FMT_I420) {
                             const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
-                            mbar_arrive_expect_tx(&full[slot], p.copy_bytes + 2 * p.chroma_copy_bytes);
-                            bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
-                            bulk_g2s(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
-                            bulk_g2s(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.chroma_copy_bytes, &full[slot]);
-                        } else {
-                            mbar_arrive_expect_tx(&full[slot], p.copy_bytes);
-                            bulk_g2s(dst, src, p.copy_bytes, &full[slot]);
+                            warp_copy_unaligned(dst + p.u_slot_off, base_a + p.u_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
+                            warp_copy_unaligned(dst + p.v_slot_off, base_a + p.v_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
                         }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&full[slot]);
+                        __syncwarp();
+                        seq += 1; ra += 1; did = true;
                     }
-                    __syncwarp();
-                    // A waiter tells phases apart by parity only, so it may look at full[slot] for sequence q only once
-                    // q has been armed (which implies q - S has completed): publish after every lane has armed its row.
-                    if (lane == 0) { __threadfence_block(); *staged = seq + k; }
-                    seq += k; r0 += (int)k;
                 }
-            } else {
-                for (int r = 0; r < n; ++r, ++seq) {
-                    const int row = p.sparse ? src_row_of(p, a + ((uint32_t)r >> 1)) + (r & 1) : ylo + r;
-                    const uint32_t slot = seq & smask;
-                    if (seq >= S) {
-                        while (seq - S >= min_rel) {                   // slot still holds a row somebody may read
-                            min_rel = __reduce_min_sync(0xffffffffu, progress[lane]);
-                            if (seq - S >= min_rel) __nanosleep(100);
-                        }
-                        __threadfence_block();
-                    }
-                    uint8_t* dst = ring + (size_t)slot * p.slot_bytes;
-                    const uint8_t* src = base + (size_t)row * p.src_stride;
-                    const uint32_t nb = (FMT == FMT_RGB8) ? p.src_w * 3 : (FMT == FMT_RGBA8 ? p.src_w * 4 : p.src_w);
-                    warp_copy_unaligned(dst, src, nb, lane);
-                    if constexpr (FMT == FMT_I420) {
-                        const uint32_t cr = min((uint32_t)row >> 1, p.chroma_h - 1);
-                        warp_copy_unaligned(dst + p.u_slot_off, base + p.u_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
-                        warp_copy_unaligned(dst + p.v_slot_off, base + p.v_off + (size_t)cr * p.chroma_pitch, p.src_w >> 1, lane);
-                    }
-                    __syncwarp();
-                    if (lane == 0) { mbar_arrive(&full[slot]); __threadfence_block(); *staged = seq + 1; }
+                if (ra == na) { a_open = false; if (fa == f_last) a_done = true; else ++fa; }
+            }
+            // Publish the records of the leading rows whose two source rows are armed by now (a waiter tells barrier
+            // phases apart by parity only, so it may look at full[slot] for sequence q only once q has been armed, which
+            // implies q - S has completed) and whose entry is free: row n - kRecs is behind every consumer warp.
+            {
+                const bool ok = in_item && (unsigned long long)n_pub + lane < (unsigned long long)min_n + kRecs &&
+                                (!inside || q0 + 1 < seq);
+                const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+                const uint32_t cnt = bal == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~bal) - 1u;
+                if (lane < cnt) {
+                    const uint32_t e = (n_pub + lane) & (kRecs - 1);
+                    const uint32_t s0 = q0 & smask, s1 = (q0 + 1) & smask;
+                    uint4 r0, r1;
+                    r0.x = p.ring_off + s0 * p.slot_bytes; r0.y = p.ring_off + s1 * p.slot_bytes;
+                    r0.z = __float_as_uint(yd);
+                    r0.w = (inside ? 1u : 0u) | (((q0 >> p.s_log2) & 1u) << 1) | ((((q0 + 1) >> p.s_log2) & 1u) << 2);
+                    r1.x = smem_u32(&full[s0]); r1.y = smem_u32(&full[s1]);
+                    const unsigned long long op = reinterpret_cast<unsigned long long>(p.out) +
+                                                  ((unsigned long long)fr * 3 * plane + (unsigned long long)h * p.dst_w) * ESZ;
+                    r1.z = (uint32_t)op; r1.w = (uint32_t)(op >> 32);
+                    recs[2 * e] = r0; recs[2 * e + 1] = r1;
+                    q0s[e] = q0;
+#ifdef TK_B200_CHECKED
+                    chk[3 * e] = fr; chk[3 * e + 1] = (uint32_t)y; chk[3 * e + 2] = n_pub + lane;
+#endif
+                }
+                __syncwarp();
+                if (cnt) {
+                    if (lane == 0) { __threadfence_block(); *rec_ready = n_pub + cnt; }
+                    n_pub += cnt; hr += cnt; did = true;
+                    if (hr == h1r) { r_open = false; seqbase_r += (uint32_t)nrows_r; ++fr; }
                 }
             }
+            if (!did) __nanosleep(64);
         }
         asm volatile("griddepcontrol.wait;" ::: "memory");
         return;
     }
 
     // ======================= consumer warps ======================================
+    // Warp (cy, *) produces the CTA's rows cy, cy + ty, ...  Before a row it publishes the row number (everything its
+    // earlier rows read is released), takes the row's record, waits for the two source rows on their `full` barriers
+    // and computes.  There is no CTA-wide barrier after set-up.
     const uint32_t cx = tid % p.tx, cy = tid / p.tx, lane = tid & 31;
-    uint32_t rel = 0;                    // next sequence number this warp has not released yet
-    auto pass_to = [&](uint32_t target) {        // release every sequence below `target`
-        __syncwarp();                            // all lanes are done reading the rows being released
-        if (lane == 0) { __threadfence_block(); progress[tid >> 5] = target; }
-        rel = target;
-    };
 
     // Pad rows/pixels (letterbox) carry the same normalisation as real pixels.
     float padn[3];
@@ -488,180 +562,155 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     for (int c = 0; c < 3; ++c) padn[c] = norm_only<EXACT>(p, c, p.pad_value);
 
     const uint32_t Q = p.tab_w >> 2;
-    const size_t plane = (size_t)p.dst_w * p.dst_h;
-    constexpr uint32_t ESZ = F16 ? 2 : 4;
-    uint32_t seq_base = 0;               // ring sequence number of the current item's first source row
+#ifdef TK_B200_CHECKED
+    volatile uint32_t* chk = reinterpret_cast<volatile uint32_t*>(smem + kSmemChk);
+    auto frame_ptr = [&](uint32_t f) -> const uint8_t* {
+        return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
+    };
+#endif
 
-    // A warp takes RPI consecutive output rows per iteration (hb .. hb+RPI-1, then hb += RPI * ty).
-    for (uint32_t f = f_first; f <= f_last; ++f) {
-        uint32_t h0, h1; item_rows(f, h0, h1);
-        int ylo, nrows; uint32_t a_first; item_src_rows(p, h0, h1, ylo, nrows, a_first);
-        for (uint32_t hb = h0 + RPI * cy; hb < h1; hb += RPI * p.ty) {
-            bool vin[RPI];
-            float yd[RPI], omy[RPI];
-            const uint8_t* row0[RPI];
-            const uint8_t* row1[RPI];
-            uint8_t* rowp[RPI];                  // byte address of the output row in tensor plane 0 of frame f
-            bool released = false;
+    for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+        __syncwarp();                            // all lanes are done reading the rows being released
+        if (lane == 0) { __threadfence_block(); progress[tid >> 5] = n; }
+        while (*rec_ready <= n) __nanosleep(32);
+        __threadfence_block();
+        const uint32_t e = n & (kRecs - 1);
+        const uint4 ra = recs[2 * e], rb = recs[2 * e + 1];
+        const bool vin = !LBOX || (ra.w & 1u);
+        const float yd = __uint_as_float(ra.z), omy = __fsub_rn(1.0f, yd);
+        const uint8_t* row0 = smem + ra.x;
+        const uint8_t* row1 = smem + ra.y;
+        uint8_t* rowp = reinterpret_cast<uint8_t*>(((unsigned long long)rb.w << 32) | rb.z);   // output row, tensor plane 0
+        if (vin) {
+            mbar_wait_backoff_addr(rb.x, (ra.w >> 1) & 1u);
+            mbar_wait_backoff_addr(rb.y, (ra.w >> 2) & 1u);
+        }
 #ifdef TK_B200_CHECKED
-            int ysrc[RPI];
+        TK_DEV_ASSERT(chk[3 * e + 2] == n && n < *rec_ready);                            // the record is this row's
+        TK_DEV_ASSERT(ra.x >= p.ring_off && ra.x + p.slot_bytes <= p.ring_off + S * p.slot_bytes && (ra.x - p.ring_off) % p.slot_bytes == 0);
+        TK_DEV_ASSERT(ra.y >= p.ring_off && ra.y + p.slot_bytes <= p.ring_off + S * p.slot_bytes && (ra.y - p.ring_off) % p.slot_bytes == 0);
+        const uint32_t chk_f = chk[3 * e];
+        const int chk_y = (int)chk[3 * e + 1];
+        if (vin) {
+            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y, row0, lane);
+            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y + 1, row1, lane);
+        }
 #endif
+        for (uint32_t q = cx; q < Q; q += p.tx) {
+            const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+            const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
+            if constexpr (AR == AR_HALF) {
+                const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
+                const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
+                const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                const __half2 yd2 = __float2half2_rn(yd);
+                uint32_t org[4], obb[4];
+                if (vin) {
 #pragma unroll
-            for (int r = 0; r < RPI; ++r) {
-                const uint32_t h = hb + r;
-                vin[r] = h < h1 && (!LBOX || (h - p.pad_top) < p.new_h);
-                yd[r] = 0.0f; omy[r] = 1.0f;
-                row0[r] = ring; row1[r] = ring;
-                rowp[r] = static_cast<uint8_t*>(p.out) + ((size_t)f * 3 * plane + (size_t)h * p.dst_w) * ESZ;
-                if (vin[r]) {
-                    float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));
-                    int y = min(__float2int_rz(gy), (int)p.src_h - 2);
-                    yd[r] = __fsub_rn(gy, (float)y);
-                    omy[r] = __fsub_rn(1.0f, yd[r]);
-                    const uint32_t q0 = seq_base + (p.sparse ? 2u * (h - a_first) : (uint32_t)(y - ylo)), q1 = q0 + 1;
-                    // release what lies below the FIRST row of the group only: the later rows read at or above it
-                    if (!released) { if (rel != q0) pass_to(q0); released = true; }
-                    row0[r] = ring + (size_t)(q0 & smask) * p.slot_bytes;
-                    row1[r] = ring + (size_t)(q1 & smask) * p.slot_bytes;
-                    while (*staged <= q1) __nanosleep(32);
-                    __threadfence_block();
-                    mbar_wait_backoff(&full[q0 & smask], (q0 >> p.s_log2) & 1u);
-                    mbar_wait_backoff(&full[q1 & smask], (q1 >> p.s_log2) & 1u);
-#ifdef TK_B200_CHECKED
-                    ysrc[r] = y;
-                    TK_DEV_ASSERT(q1 < *staged && q0 >= rel && q1 - rel < S);        // inside the window this warp holds
-                    TK_DEV_ASSERT((size_t)(q1 & smask) * p.slot_bytes + p.slot_bytes <= (size_t)S * p.slot_bytes);
-                    check_ring_row<FMT>(p, frame_ptr(f), y, row0[r], lane);
-                    check_ring_row<FMT>(p, frame_ptr(f), y + 1, row1[r], lane);
-#endif
+                    for (int j = 0; j < 4; ++j) {
+                        if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
+                        uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
+                        fetch_pairs_half<FMT>(row0, xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
+                        fetch_pairs_half<FMT>(row1, xbs[j], bl_rg, bl_bb, br_rg, br_bb);
+                        const __half2 xd2 = as_h2(xds[j]);
+                        org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                        obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
                 }
-            }
-            for (uint32_t q = cx; q < Q; q += p.tx) {
-                const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
-                const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
-                if constexpr (AR == AR_HALF) {
-                    const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
-                    const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
-                    const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                    const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+                // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
+                const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
+                const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
+                const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
+                uint8_t* qp = rowp + (size_t)(4u * q) * 2;
+                const uint2 vs[3] = {vr, vg, vb};
+                if (p.vec_store) {
 #pragma unroll
-                    for (int r = 0; r < RPI; ++r) {
-                        if (hb + r >= h1) break;
-                        const __half2 yd2 = __float2half2_rn(yd[r]);
-                        uint32_t org[4], obb[4];
-                        if (vin[r]) {
+                    for (int c = 0; c < 3; ++c) __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), vs[c]);
+                } else {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
-                                uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
-                                fetch_pairs_half<FMT>(row0[r], xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
-                                fetch_pairs_half<FMT>(row1[r], xbs[j], bl_rg, bl_bb, br_rg, br_bb);
-                                const __half2 xd2 = as_h2(xds[j]);
-                                org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                                obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
-                            }
-                        } else {
+                    for (int c = 0; c < 3; ++c) {
+                        const uint32_t wds[2] = {vs[c].x, vs[c].y};
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
-                        }
-                        // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
-                        const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
-                        const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
-                        const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
-                        uint8_t* qp = rowp[r] + (size_t)(4u * q) * 2;
-                        const uint2 vs[3] = {vr, vg, vb};
-                        if (p.vec_store) {
+                        for (int j = 0; j < 4; ++j)
+                            if (4u * q + j < p.dst_w)
+                                reinterpret_cast<uint16_t*>(qp + p.cplane[c])[j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                    }
+                }
+            } else {
+                const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
+                // column constants of the quad, as two packed pairs: xd, 1 - xd, and (EXACT) their -2^23 multiples
+                float2 xd2[2] = {f2(xd4.x, xd4.y), f2(xd4.z, xd4.w)}, omx2[2], cxd2[2], comx2[2];
 #pragma unroll
-                            for (int c = 0; c < 3; ++c) __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), vs[c]);
-                        } else {
+                for (int jp = 0; jp < 2; ++jp) {
+                    omx2[jp] = add2(f2s(1.0f), f2(-xd2[jp].x, -xd2[jp].y));      // 1 - xd
+                    cxd2[jp] = xd2[jp]; comx2[jp] = omx2[jp];
+                    if constexpr (EXACT) { cxd2[jp] = mul2(xd2[jp], f2s(-kBias)); comx2[jp] = mul2(omx2[jp], f2s(-kBias)); }
+                }
+                float o[3][4];
+                if (vin) {
 #pragma unroll
-                            for (int c = 0; c < 3; ++c) {
-                                const uint32_t wds[2] = {vs[c].x, vs[c].y};
+                    for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
+                        float ma[4][3], mb[4][3];
+                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j], 0) : xbs[j], ma);
+                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
 #pragma unroll
-                                for (int j = 0; j < 4; ++j)
-                                    if (4u * q + j < p.dst_w)
-                                        reinterpret_cast<uint16_t*>(qp + p.cplane[c])[j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
-                            }
+                        for (int c = 0; c < 3; ++c) {
+                            const float2 v = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
+                                                                f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2[j >> 1],
+                                                                omx2[j >> 1], cxd2[j >> 1], comx2[j >> 1], yd, omy);
+                            o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : v.x;
+                            o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : v.y;
                         }
                     }
                 } else {
-                    const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
-                    // column constants of the quad, as two packed pairs: xd, 1 - xd, and (EXACT) their -2^23 multiples
-                    float2 xd2[2] = {f2(xd4.x, xd4.y), f2(xd4.z, xd4.w)}, omx2[2], cxd2[2], comx2[2];
 #pragma unroll
-                    for (int jp = 0; jp < 2; ++jp) {
-                        omx2[jp] = add2(f2s(1.0f), f2(-xd2[jp].x, -xd2[jp].y));      // 1 - xd
-                        cxd2[jp] = xd2[jp]; comx2[jp] = omx2[jp];
-                        if constexpr (EXACT) { cxd2[jp] = mul2(xd2[jp], f2s(-kBias)); comx2[jp] = mul2(omx2[jp], f2s(-kBias)); }
-                    }
+                    for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
+                }
+                // one 64-bit address per quad; the channel planes are constant byte offsets from it
+                uint8_t* qp = rowp + (size_t)(4u * q) * ESZ;
+                if (p.vec_store) {
 #pragma unroll
-                    for (int r = 0; r < RPI; ++r) {
-                        if (hb + r >= h1) break;
-                        float o[3][4];
-                        if (vin[r]) {
-#pragma unroll
-                            for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
-                                float ma[4][3], mb[4][3];
-                                fetch_quad<FMT>(p, row0[r], row1[r], LBOX ? max(xbs[j], 0) : xbs[j], ma);
-                                fetch_quad<FMT>(p, row0[r], row1[r], LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
-#pragma unroll
-                                for (int c = 0; c < 3; ++c) {
-                                    const float2 v = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
-                                                                        f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2[j >> 1],
-                                                                        omx2[j >> 1], cxd2[j >> 1], comx2[j >> 1], yd[r], omy[r]);
-                                    o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : v.x;
-                                    o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : v.y;
-                                }
-                            }
+                    for (int c = 0; c < 3; ++c) {
+                        if constexpr (F16) {
+                            __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
+                            __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
+                            uint2 v;
+                            v.x = *reinterpret_cast<uint32_t*>(&lo);
+                            v.y = *reinterpret_cast<uint32_t*>(&hi);
+                            __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), v);
                         } else {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
+                            __stcs(reinterpret_cast<float4*>(qp + p.cplane[c]), make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
                         }
-                        // one 64-bit address per quad; the channel planes are constant byte offsets from it
-                        uint8_t* qp = rowp[r] + (size_t)(4u * q) * ESZ;
-                        if (p.vec_store) {
+                    }
+                } else {
 #pragma unroll
-                            for (int c = 0; c < 3; ++c) {
-                                if constexpr (F16) {
-                                    __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
-                                    __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
-                                    uint2 v;
-                                    v.x = *reinterpret_cast<uint32_t*>(&lo);
-                                    v.y = *reinterpret_cast<uint32_t*>(&hi);
-                                    __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), v);
-                                } else {
-                                    __stcs(reinterpret_cast<float4*>(qp + p.cplane[c]), make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
-                                }
-                            }
-                        } else {
+                    for (int c = 0; c < 3; ++c) {
 #pragma unroll
-                            for (int c = 0; c < 3; ++c) {
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) {
-                                    if (4u * q + j < p.dst_w) {
-                                        if constexpr (F16) reinterpret_cast<__half*>(qp + p.cplane[c])[j] = __float2half_rn(o[c][j]);
-                                        else reinterpret_cast<float*>(qp + p.cplane[c])[j] = o[c][j];
-                                    }
-                                }
+                        for (int j = 0; j < 4; ++j) {
+                            if (4u * q + j < p.dst_w) {
+                                if constexpr (F16) reinterpret_cast<__half*>(qp + p.cplane[c])[j] = __float2half_rn(o[c][j]);
+                                else reinterpret_cast<float*>(qp + p.cplane[c])[j] = o[c][j];
                             }
                         }
                     }
                 }
             }
-#ifdef TK_B200_CHECKED
-            // ... and still hold them now that every pixel of the group has been computed (nothing overwrote a slot early)
-#pragma unroll
-            for (int r = 0; r < RPI; ++r)
-                if (vin[r]) {
-                    check_ring_row<FMT>(p, frame_ptr(f), ysrc[r], row0[r], lane);
-                    check_ring_row<FMT>(p, frame_ptr(f), ysrc[r] + 1, row1[r], lane);
-                }
-#endif
         }
-        seq_base += (uint32_t)nrows;
+#ifdef TK_B200_CHECKED
+        // ... and still hold them now that every pixel of the row has been computed (nothing overwrote a slot early)
+        if (vin) {
+            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y, row0, lane);
+            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y + 1, row1, lane);
+        }
+#endif
     }
-    pass_to(0xffffffffu);                        // done: nothing this warp could still read
-    if (p.trace.buf && tid == 0) { t_trace[1] = gtimer(); trace_put(p.trace, 1u, blockIdx.x, (uint32_t)(g1 - g0), t_trace, 2); }
+    __syncwarp();                                // done: nothing this warp could still read
+    if (lane == 0) { __threadfence_block(); progress[tid >> 5] = 0xffffffffu; }
+    if (p.trace.buf && tid == 0) { t_trace[1] = gtimer(); trace_put(p.trace, 1u, blockIdx.x, nrows_cta, t_trace, 2); }
     // Possibly launched early behind an unrelated kernel (see launch_variant): complete only after it has.
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
@@ -890,7 +939,7 @@ tk_error_code_t tkb::preprocess_batch_impl(const tk_b200_preprocess_batch_params
               (k.chroma_copy_bytes <= k.chroma_pitch);
 
     k.tab_w = (k.dst_w + 3) & ~3u;
-    k.ring_off = (512 + 8 * k.tab_w + 127) & ~127u;
+    k.ring_off = (kSmemTabs + 8 * k.tab_w + 127) & ~127u;
     k.vec_store = (k.dst_w % 4 == 0) && (reinterpret_cast<uintptr_t>(prm->d_output) % 16 == 0);
 
     // Consumer shape: tx threads along x cover the row's pixel quads, ty rows in flight;
@@ -931,6 +980,10 @@ tk_error_code_t tkb::preprocess_batch_impl(const tk_b200_preprocess_batch_params
     unsigned long long max_ctas = (total_rows + per_cta_min - 1) / per_cta_min;
     const uint32_t resident = (smem <= 110 * 1024 ? 2u : 1u) * (uint32_t)dev->sm_count;
     dim3 grid((unsigned)(max_ctas < resident ? max_ctas : resident));
+    if (total_rows / grid.x >= 0x7fffffffull) {                               // the kernel counts a CTA's rows in 32 bits
+        tk_error_set_detail("%llu output rows are more than one launch takes", total_rows);
+        return TK_ERROR_NOT_IMPLEMENTED;
+    }
 
     const bool f16 = prm->output_type == TK_B200_OUT_F16;
     if ((unsigned)prm->arith > TK_B200_ARITH_HALF) return TK_ERROR_INVALID_ARGUMENT;

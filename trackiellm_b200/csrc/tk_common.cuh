@@ -167,6 +167,19 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity
         __nanosleep(64);
     }
 }
+// Same, the barrier given by its shared-window address.
+__device__ __forceinline__ void mbar_wait_backoff_addr(uint32_t addr, uint32_t parity) {
+    uint32_t ok;
+    for (;;) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) break;
+        __nanosleep(64);
+    }
+}
 // TMA 1-D bulk copy global -> shared, completion signalled on an mbarrier.
 // dst, src 16-byte aligned, bytes a multiple of 16.
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
