@@ -85,17 +85,33 @@ __device__ __forceinline__ float magic_byte(uint32_t word, uint32_t sel) {
     return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | sel));
 }
 
+// Column constants of one output pixel, worked out once per column (load_cols in the kernel) instead of once per pixel:
+//   RGB8   off = byte offset of the 4-byte word holding the left source pixel's first byte, aux = its bit position in that word
+//   RGBA8  off = byte offset of the left source pixel
+//   I420   off = luma index of the left source pixel, aux = chroma index of the left pixel, bit 31: the right pixel's is one more
+template <int FMT>
+__device__ __forceinline__ void col_consts(const PreK& p, int xb, int& off, uint32_t& aux) {
+    if constexpr (FMT == FMT_RGB8) { off = xb & ~3; aux = ((uint32_t)xb & 3u) << 3; }
+    else if constexpr (FMT == FMT_RGBA8) { off = xb; aux = 0; }
+    else {
+        const int cw = (int)(p.src_w >> 1);
+        off = xb;
+        const int c0 = min(xb >> 1, cw - 1), c1 = min((xb + 1) >> 1, cw - 1);
+        aux = (uint32_t)c0 | ((uint32_t)(c1 - c0) << 31);                 // c1 - c0 is 0 or 1
+    }
+}
+
 // Fetch the 2x2 source neighbourhood of one output pixel as biased floats
 // m[k][c] = 2^23 + value, k = {top-left, top-right, bottom-left, bottom-right}.
 template <int FMT>
 __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, const uint8_t* row1,
-                                           int xb, float (&m)[4][3]) {
+                                           int off, uint32_t aux, float (&m)[4][3]) {
     if constexpr (FMT == FMT_RGB8) {
-        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + (xb & ~3));
-        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + (xb & ~3));
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + off);
+        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + off);
         uint32_t a0 = a[0], a1 = a[1], a2 = a[2];
         uint32_t b0 = b[0], b1 = b[1], b2 = b[2];
-        uint32_t sh = (uint32_t)xb << 3;                 // funnel shift uses the low 5 bits
+        const uint32_t sh = aux;                         // 0, 8, 16, 24
         uint32_t alo = __funnelshift_r(a0, a1, sh), ahi = __funnelshift_r(a1, a2, sh);
         uint32_t blo = __funnelshift_r(b0, b1, sh), bhi = __funnelshift_r(b1, b2, sh);
         m[0][0] = magic_byte(alo, 0); m[0][1] = magic_byte(alo, 1); m[0][2] = magic_byte(alo, 2);
@@ -103,8 +119,8 @@ __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, c
         m[2][0] = magic_byte(blo, 0); m[2][1] = magic_byte(blo, 1); m[2][2] = magic_byte(blo, 2);
         m[3][0] = magic_byte(blo, 3); m[3][1] = magic_byte(bhi, 0); m[3][2] = magic_byte(bhi, 1);
     } else if constexpr (FMT == FMT_RGBA8) {
-        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + xb);
-        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + xb);
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + off);
+        const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + off);
         uint32_t a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -112,14 +128,13 @@ __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, c
             m[2][c] = magic_byte(b0, c); m[3][c] = magic_byte(b1, c);
         }
     } else {
-        // I420: xb is the luma pixel index.  BT.601 full range, 16.16 fixed point,
+        // I420: off is the luma pixel index.  BT.601 full range, 16.16 fixed point,
         // nearest chroma — the integer arithmetic of oracle_i420_to_rgb8.
-        const int cw = (int)(p.src_w >> 1);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const uint8_t* row = (k & 2) ? row1 : row0;
-            int x = xb + (k & 1);
-            int cx = min(x >> 1, cw - 1);
+            const int x = off + (k & 1);
+            const int cx = (int)((aux & 0x7fffffffu) + ((k & 1) ? (aux >> 31) : 0u));
             // (yy*65536 + K*(c-128) + 32768) >> 16 == yy + ((K*c + 32768 - 128*K) >> 16): the luma term is a
             // multiple of 65536 and >> is a floor.  add + clamp to [0, 255] is one VIADDMNMX.RELU (DPX).
             const int yy = row[x];
@@ -250,18 +265,18 @@ __device__ __forceinline__ void warp_copy_unaligned(uint8_t* dst, const uint8_t*
 // pairs, 0x6400 | byte == 1024 + byte exactly, differences exact, lerps and the
 // normalisation in HFMA2 — half the math instructions of the fp32 lerp.  Error bound: DESIGN.md §3.
 template <int FMT>
-__device__ __forceinline__ void fetch_pairs_half(const uint8_t* row, int xb, uint32_t& l_rg, uint32_t& l_bb,
+__device__ __forceinline__ void fetch_pairs_half(const uint8_t* row, int off, uint32_t aux, uint32_t& l_rg, uint32_t& l_bb,
                                                  uint32_t& r_rg, uint32_t& r_bb) {
     const uint32_t C64 = 0x64646464u;
     uint32_t lw, rw;                                   // words starting at the left / right pixel
     if constexpr (FMT == FMT_RGB8) {
-        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + (xb & ~3));
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + off);
         const uint32_t a0 = a[0], a1 = a[1], a2 = a[2];
-        const uint32_t sh = (uint32_t)xb << 3;
+        const uint32_t sh = aux;
         lw = __funnelshift_r(a0, a1, sh);
         rw = __funnelshift_r(lw, __funnelshift_r(a1, a2, sh), 24);
     } else {
-        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + xb);
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(row + off);
         lw = a[0]; rw = a[1];
     }
     l_rg = __byte_perm(lw, C64, 0x4140); l_bb = __byte_perm(lw, C64, 0x4242);
@@ -569,19 +584,55 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     };
 #endif
 
-    for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+    // Column constants of a quad of four output pixels (row-independent).
+    struct Cols {
+        int off[4]; uint32_t aux[4];             // col_consts
+        uint32_t padmask;                        // letterbox: bit j = pixel j is padding
+        float2 xd2[2], omx2[2], cxd2[2], comx2[2];   // fp32 arithmetic: xd, 1 - xd, and (EXACT) their -2^23 multiples, as packed pairs
+        uint32_t xdh[4];                         // HALF: half2 {xd, xd}
+    };
+    auto load_cols = [&](uint32_t q, Cols& c) {
+        const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
+        const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
+        c.padmask = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (LBOX && xbs[j] < 0) c.padmask |= 1u << j;
+            col_consts<FMT>(p, LBOX ? max(xbs[j], 0) : xbs[j], c.off[j], c.aux[j]);
+        }
+        if constexpr (AR == AR_HALF) {
+            const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
+            c.xdh[0] = xd4.x; c.xdh[1] = xd4.y; c.xdh[2] = xd4.z; c.xdh[3] = xd4.w;
+        } else {
+            const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
+            c.xd2[0] = f2(xd4.x, xd4.y); c.xd2[1] = f2(xd4.z, xd4.w);
+#pragma unroll
+            for (int jp = 0; jp < 2; ++jp) {
+                c.omx2[jp] = add2(f2s(1.0f), f2(-c.xd2[jp].x, -c.xd2[jp].y));      // 1 - xd
+                c.cxd2[jp] = c.xd2[jp]; c.comx2[jp] = c.omx2[jp];
+                if constexpr (EXACT) { c.cxd2[jp] = mul2(c.xd2[jp], f2s(-kBias)); c.comx2[jp] = mul2(c.omx2[jp], f2s(-kBias)); }
+            }
+        }
+    };
+
+    // Row set-up: publish the row number, take the record, wait for the two source rows.
+    struct Row { const uint8_t* row0; const uint8_t* row1; uint8_t* out; float yd, omy; bool vin;
+#ifdef TK_B200_CHECKED
+                 uint32_t chk_f; int chk_y;
+#endif
+    };
+    auto begin_row = [&](uint32_t n, Row& r) {
         __syncwarp();                            // all lanes are done reading the rows being released
         if (lane == 0) { __threadfence_block(); progress[tid >> 5] = n; }
         while (*rec_ready <= n) __nanosleep(32);
         __threadfence_block();
         const uint32_t e = n & (kRecs - 1);
         const uint4 ra = recs[2 * e], rb = recs[2 * e + 1];
-        const bool vin = !LBOX || (ra.w & 1u);
-        const float yd = __uint_as_float(ra.z), omy = __fsub_rn(1.0f, yd);
-        const uint8_t* row0 = smem + ra.x;
-        const uint8_t* row1 = smem + ra.y;
-        uint8_t* rowp = reinterpret_cast<uint8_t*>(((unsigned long long)rb.w << 32) | rb.z);   // output row, tensor plane 0
-        if (vin) {
+        r.vin = !LBOX || (ra.w & 1u);
+        r.yd = __uint_as_float(ra.z); r.omy = __fsub_rn(1.0f, r.yd);
+        r.row0 = smem + ra.x; r.row1 = smem + ra.y;
+        r.out = reinterpret_cast<uint8_t*>(((unsigned long long)rb.w << 32) | rb.z);       // output row, tensor plane 0
+        if (r.vin) {
             mbar_wait_backoff_addr(rb.x, (ra.w >> 1) & 1u);
             mbar_wait_backoff_addr(rb.y, (ra.w >> 2) & 1u);
         }
@@ -589,124 +640,137 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         TK_DEV_ASSERT(chk[3 * e + 2] == n && n < *rec_ready);                            // the record is this row's
         TK_DEV_ASSERT(ra.x >= p.ring_off && ra.x + p.slot_bytes <= p.ring_off + S * p.slot_bytes && (ra.x - p.ring_off) % p.slot_bytes == 0);
         TK_DEV_ASSERT(ra.y >= p.ring_off && ra.y + p.slot_bytes <= p.ring_off + S * p.slot_bytes && (ra.y - p.ring_off) % p.slot_bytes == 0);
-        const uint32_t chk_f = chk[3 * e];
-        const int chk_y = (int)chk[3 * e + 1];
-        if (vin) {
-            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y, row0, lane);
-            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y + 1, row1, lane);
+        r.chk_f = chk[3 * e]; r.chk_y = (int)chk[3 * e + 1];
+        if (r.vin) {
+            check_ring_row<FMT>(p, frame_ptr(r.chk_f), r.chk_y, r.row0, lane);
+            check_ring_row<FMT>(p, frame_ptr(r.chk_f), r.chk_y + 1, r.row1, lane);
         }
 #endif
-        for (uint32_t q = cx; q < Q; q += p.tx) {
-            const int4 xb4 = reinterpret_cast<const int4*>(xb_tab)[q];
-            const int xbs[4] = {xb4.x, xb4.y, xb4.z, xb4.w};
-            if constexpr (AR == AR_HALF) {
-                const uint4 xd4 = reinterpret_cast<const uint4*>(xd_tab)[q];
-                const uint32_t xds[4] = {xd4.x, xd4.y, xd4.z, xd4.w};
-                const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
-                const __half2 yd2 = __float2half2_rn(yd);
-                uint32_t org[4], obb[4];
-                if (vin) {
+    };
+    auto end_row = [&](const Row& r) {
+#ifdef TK_B200_CHECKED
+        // ... and still hold them now that every pixel of the row has been computed (nothing overwrote a slot early)
+        if (r.vin) {
+            check_ring_row<FMT>(p, frame_ptr(r.chk_f), r.chk_y, r.row0, lane);
+            check_ring_row<FMT>(p, frame_ptr(r.chk_f), r.chk_y + 1, r.row1, lane);
+        }
+#endif
+    };
+
+    // Four consecutive output pixels x three channels of one row.
+    auto do_quad = [&](uint32_t q, const Cols& c, const Row& r) {
+        if constexpr (AR == AR_HALF) {
+            const uint32_t pad_rg = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+            const uint32_t pad_bb = h2_bits(__hfma2(__float2half2_rn(p.pad_value - 128.0f), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
+            const __half2 yd2 = __float2half2_rn(r.yd);
+            uint32_t org[4], obb[4];
+            if (r.vin) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (LBOX && xbs[j] < 0) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
-                        uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
-                        fetch_pairs_half<FMT>(row0, xbs[j], tl_rg, tl_bb, tr_rg, tr_bb);
-                        fetch_pairs_half<FMT>(row1, xbs[j], bl_rg, bl_bb, br_rg, br_bb);
-                        const __half2 xd2 = as_h2(xds[j]);
-                        org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
-                        obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
-                    }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
+                for (int j = 0; j < 4; ++j) {
+                    if (LBOX && ((c.padmask >> j) & 1u)) { org[j] = pad_rg; obb[j] = pad_bb; continue; }
+                    uint32_t tl_rg, tl_bb, tr_rg, tr_bb, bl_rg, bl_bb, br_rg, br_bb;
+                    fetch_pairs_half<FMT>(r.row0, c.off[j], c.aux[j], tl_rg, tl_bb, tr_rg, tr_bb);
+                    fetch_pairs_half<FMT>(r.row1, c.off[j], c.aux[j], bl_rg, bl_bb, br_rg, br_bb);
+                    const __half2 xd2 = as_h2(c.xdh[j]);
+                    org[j] = h2_bits(__hfma2(lerp_pair_half(tl_rg, tr_rg, bl_rg, br_rg, xd2, yd2), as_h2(p.h_scale_rg), as_h2(p.h_bias_rg)));
+                    obb[j] = h2_bits(__hfma2(lerp_pair_half(tl_bb, tr_bb, bl_bb, br_bb, xd2, yd2), as_h2(p.h_scale_bb), as_h2(p.h_bias_bb)));
                 }
-                // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
-                const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
-                const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
-                const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
-                uint8_t* qp = rowp + (size_t)(4u * q) * 2;
-                const uint2 vs[3] = {vr, vg, vb};
-                if (p.vec_store) {
+            } else {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), vs[c]);
-                } else {
+                for (int j = 0; j < 4; ++j) { org[j] = pad_rg; obb[j] = pad_bb; }
+            }
+            // regroup {R,G}/{B,B} per pixel into per-plane pixel pairs
+            const uint2 vr = make_uint2(__byte_perm(org[0], org[1], 0x5410), __byte_perm(org[2], org[3], 0x5410));
+            const uint2 vg = make_uint2(__byte_perm(org[0], org[1], 0x7632), __byte_perm(org[2], org[3], 0x7632));
+            const uint2 vb = make_uint2(__byte_perm(obb[0], obb[1], 0x5410), __byte_perm(obb[2], obb[3], 0x5410));
+            uint8_t* qp = r.out + (size_t)(4u * q) * 2;
+            const uint2 vs[3] = {vr, vg, vb};
+            if (p.vec_store) {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const uint32_t wds[2] = {vs[c].x, vs[c].y};
+                for (int ch = 0; ch < 3; ++ch) __stcs(reinterpret_cast<uint2*>(qp + p.cplane[ch]), vs[ch]);
+            } else {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (4u * q + j < p.dst_w)
-                                reinterpret_cast<uint16_t*>(qp + p.cplane[c])[j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                for (int ch = 0; ch < 3; ++ch) {
+                    const uint32_t wds[2] = {vs[ch].x, vs[ch].y};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (4u * q + j < p.dst_w)
+                            reinterpret_cast<uint16_t*>(qp + p.cplane[ch])[j] = (uint16_t)(wds[j >> 1] >> ((j & 1) * 16));
+                }
+            }
+        } else {
+            float o[3][4];
+            if (r.vin) {
+#pragma unroll
+                for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
+                    float ma[4][3], mb[4][3];
+                    fetch_quad<FMT>(p, r.row0, r.row1, c.off[j], c.aux[j], ma);
+                    fetch_quad<FMT>(p, r.row0, r.row1, c.off[j + 1], c.aux[j + 1], mb);
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) {
+                        const float2 v = blend_norm2<EXACT>(p, ch, f2(ma[0][ch], mb[0][ch]), f2(ma[1][ch], mb[1][ch]),
+                                                            f2(ma[2][ch], mb[2][ch]), f2(ma[3][ch], mb[3][ch]), c.xd2[j >> 1],
+                                                            c.omx2[j >> 1], c.cxd2[j >> 1], c.comx2[j >> 1], r.yd, r.omy);
+                        o[ch][j] = (LBOX && ((c.padmask >> j) & 1u)) ? padn[ch] : v.x;
+                        o[ch][j + 1] = (LBOX && ((c.padmask >> (j + 1)) & 1u)) ? padn[ch] : v.y;
                     }
                 }
             } else {
-                const float4 xd4 = reinterpret_cast<const float4*>(xd_tab)[q];
-                // column constants of the quad, as two packed pairs: xd, 1 - xd, and (EXACT) their -2^23 multiples
-                float2 xd2[2] = {f2(xd4.x, xd4.y), f2(xd4.z, xd4.w)}, omx2[2], cxd2[2], comx2[2];
 #pragma unroll
-                for (int jp = 0; jp < 2; ++jp) {
-                    omx2[jp] = add2(f2s(1.0f), f2(-xd2[jp].x, -xd2[jp].y));      // 1 - xd
-                    cxd2[jp] = xd2[jp]; comx2[jp] = omx2[jp];
-                    if constexpr (EXACT) { cxd2[jp] = mul2(xd2[jp], f2s(-kBias)); comx2[jp] = mul2(omx2[jp], f2s(-kBias)); }
-                }
-                float o[3][4];
-                if (vin) {
+                for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
+            }
+            // one 64-bit address per quad; the channel planes are constant byte offsets from it
+            uint8_t* qp = r.out + (size_t)(4u * q) * ESZ;
+            if (p.vec_store) {
 #pragma unroll
-                    for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
-                        float ma[4][3], mb[4][3];
-                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j], 0) : xbs[j], ma);
-                        fetch_quad<FMT>(p, row0, row1, LBOX ? max(xbs[j + 1], 0) : xbs[j + 1], mb);
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            const float2 v = blend_norm2<EXACT>(p, c, f2(ma[0][c], mb[0][c]), f2(ma[1][c], mb[1][c]),
-                                                                f2(ma[2][c], mb[2][c]), f2(ma[3][c], mb[3][c]), xd2[j >> 1],
-                                                                omx2[j >> 1], cxd2[j >> 1], comx2[j >> 1], yd, omy);
-                            o[c][j] = (LBOX && xbs[j] < 0) ? padn[c] : v.x;
-                            o[c][j + 1] = (LBOX && xbs[j + 1] < 0) ? padn[c] : v.y;
-                        }
+                for (int ch = 0; ch < 3; ++ch) {
+                    if constexpr (F16) {
+                        __half2 lo = __floats2half2_rn(o[ch][0], o[ch][1]);
+                        __half2 hi = __floats2half2_rn(o[ch][2], o[ch][3]);
+                        uint2 v;
+                        v.x = *reinterpret_cast<uint32_t*>(&lo);
+                        v.y = *reinterpret_cast<uint32_t*>(&hi);
+                        __stcs(reinterpret_cast<uint2*>(qp + p.cplane[ch]), v);
+                    } else {
+                        __stcs(reinterpret_cast<float4*>(qp + p.cplane[ch]), make_float4(o[ch][0], o[ch][1], o[ch][2], o[ch][3]));
                     }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) { o[0][j] = padn[0]; o[1][j] = padn[1]; o[2][j] = padn[2]; }
                 }
-                // one 64-bit address per quad; the channel planes are constant byte offsets from it
-                uint8_t* qp = rowp + (size_t)(4u * q) * ESZ;
-                if (p.vec_store) {
+            } else {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        if constexpr (F16) {
-                            __half2 lo = __floats2half2_rn(o[c][0], o[c][1]);
-                            __half2 hi = __floats2half2_rn(o[c][2], o[c][3]);
-                            uint2 v;
-                            v.x = *reinterpret_cast<uint32_t*>(&lo);
-                            v.y = *reinterpret_cast<uint32_t*>(&hi);
-                            __stcs(reinterpret_cast<uint2*>(qp + p.cplane[c]), v);
-                        } else {
-                            __stcs(reinterpret_cast<float4*>(qp + p.cplane[c]), make_float4(o[c][0], o[c][1], o[c][2], o[c][3]));
-                        }
-                    }
-                } else {
+                for (int ch = 0; ch < 3; ++ch) {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (4u * q + j < p.dst_w) {
-                                if constexpr (F16) reinterpret_cast<__half*>(qp + p.cplane[c])[j] = __float2half_rn(o[c][j]);
-                                else reinterpret_cast<float*>(qp + p.cplane[c])[j] = o[c][j];
-                            }
+                    for (int j = 0; j < 4; ++j) {
+                        if (4u * q + j < p.dst_w) {
+                            if constexpr (F16) reinterpret_cast<__half*>(qp + p.cplane[ch])[j] = __float2half_rn(o[ch][j]);
+                            else reinterpret_cast<float*>(qp + p.cplane[ch])[j] = o[ch][j];
                         }
                     }
                 }
             }
         }
-#ifdef TK_B200_CHECKED
-        // ... and still hold them now that every pixel of the row has been computed (nothing overwrote a slot early)
-        if (vin) {
-            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y, row0, lane);
-            check_ring_row<FMT>(p, frame_ptr(chk_f), chk_y + 1, row1, lane);
+    };
+
+    if (Q <= p.tx) {
+        // One quad per thread and row (rows of <= 640 pixels): its column constants stay in registers for the whole run —
+        // two 16-byte table loads, six packed fp32 and a dozen ALU-pipe instructions less per row.
+        Cols c{};
+        const bool has = cx < Q;
+        if (has) load_cols(cx, c);
+        for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+            Row r; begin_row(n, r);
+            if (has) do_quad(cx, c, r);
+            end_row(r);
         }
-#endif
+    } else {
+        for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+            Row r; begin_row(n, r);
+            for (uint32_t q = cx; q < Q; q += p.tx) {
+                Cols c{};
+                load_cols(q, c);
+                do_quad(q, c, r);
+            }
+            end_row(r);
+        }
     }
     __syncwarp();                                // done: nothing this warp could still read
     if (lane == 0) { __threadfence_block(); progress[tid >> 5] = 0xffffffffu; }
