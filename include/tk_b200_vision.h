@@ -180,6 +180,17 @@ typedef struct {
 
 TK_NODISCARD tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* params, cudaStream_t stream);
 
+/* The same NMS for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same parameters and
+ * results, bit for bit, as tk_kernels_nms_classwise; calls no cudaMalloc / cudaFree / stream-ordered allocator: the
+ * per-CTA work areas live in a file-scope device array of 6.1 MiB (8 x nms work area of 16384 candidates) that every
+ * GPU that loads the library holds until the process exits.  max_candidates above
+ * tk_b200_nms_classwise_static_max_candidates() (16384) -> TK_ERROR_BUFFER_TOO_SMALL with a detail text.
+ * All calls on a device share the array: calls that overlap on the GPU (two streams, two threads) race - the caller
+ * serialises them.  Nothing in the array has to be cleared between calls (every frame initialises what it reads). */
+TK_NODISCARD tk_error_code_t tk_b200_nms_classwise_static(const tk_b200_nms_params_t* params, cudaStream_t stream);
+uint32_t tk_b200_nms_classwise_static_max_candidates(void);
+
 /* Decode + class-wise NMS of whole frames in ONE kernel (completes src/vision/tk_object_detector.c:343-357 in one
  * pass).  Same results, bit for bit, as tk_kernels_decode_detections followed by tk_kernels_nms_classwise;
  * d_candidates / d_counts receive the intermediate list exactly as decode leaves it.  Two layouts:

@@ -203,6 +203,8 @@ def lib() -> C.CDLL:
         _lib.tk_object_detector_update_thresholds.restype = None
         _lib.tk_object_detector_update_thresholds.argtypes = [C.c_void_p, C.c_float, C.c_float]
         _lib.tk_object_detector_destroy.restype = None
+        _lib.tk_b200_nms_classwise_static_max_candidates.restype = C.c_uint32
+        _lib.tk_b200_nms_classwise_static_max_candidates.argtypes = []
         _lib.tk_b200_host_free.argtypes = [C.c_void_p]
         _lib.tk_b200_host_free.restype = None
     return _lib

@@ -32,6 +32,8 @@
 //     src/vision/tk_object_detector.c:339-355).
 #include "nms_frame.cuh"
 
+#include <mutex>
+
 namespace tkb {
 
 // One CTA per frame while the batch fits one wave; larger batches loop (every exit of nms_frame is CTA-uniform).
@@ -140,4 +142,79 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
     k.select = 2;
     nms_kernel<<<sms, kNmsThreads, smem, stream>>>(k);
     return launch_status("nms_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------------------------ //
+// tk_b200_nms_classwise_static — the same NMS with NO allocation of any kind (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The per-CTA work areas of nms_global_kernel live in a file-scope device array
+// instead of stream-ordered scratch.  Every GPU that loads the library holds the array (kNmsStaticBytes, 6.1 MiB) until
+// the process exits; every call on a device shares it, so calls that overlap on the GPU (two streams, two host
+// threads) race — serialise them.  The array keeps the last call's contents: nms_frame initialises every word it
+// reads (keys, boxes, masks, the kept bitmap) per frame, nothing has to start at zero.
+// ------------------------------------------------------------------------------------------------------------------ //
+namespace tkb {
+static constexpr uint32_t kNmsStaticMaxK = 16384;                              // most candidates per frame this entry point takes
+static constexpr uint32_t kNmsStaticAreas = 8;                                 // work areas at that size (more when frames are smaller)
+static constexpr size_t kNmsStaticBytes = (size_t)kNmsStaticAreas * ((size_t)kNmsStaticMaxK * 49 + kNmsStaticMaxK / 8);
+static_assert(kNmsStaticBytes == kNmsStaticAreas * nms_smem_bytes(kNmsStaticMaxK), "work-area layout of nms_frame.cuh");
+static __device__ __align__(256) uint8_t g_nms_static_scratch[kNmsStaticBytes];
+
+// Device address of the array on the CURRENT device, looked up once per device (in host code the array's name is a
+// host-side stand-in, not something a kernel can be handed).
+static tk_error_code_t nms_static_scratch(uint8_t** out) {
+    static std::mutex mu;
+    static uint8_t* addr[64] = {};
+    int dev = -1;
+    if (!device_info(&dev)) return TK_ERROR_GPU_DEVICE_NOT_FOUND;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_nms_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            tk_error_set_detail("nms (static scratch): cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return TK_ERROR_GPU_CUDA_ERROR;
+        }
+        addr[dev] = static_cast<uint8_t*>(ptr);
+    }
+    *out = addr[dev];
+    return TK_SUCCESS;
+}
+}  // namespace tkb
+
+extern "C" uint32_t tk_b200_nms_classwise_static_max_candidates(void) { return tkb::kNmsStaticMaxK; }
+
+extern "C" tk_error_code_t tk_b200_nms_classwise_static(const tk_b200_nms_params_t* p, cudaStream_t stream) {
+    if (!p || !p->d_counts || !p->d_num_detections || (!p->d_candidates && p->max_candidates) ||
+        (!p->d_detections && p->max_detections))
+        return TK_ERROR_INVALID_ARGUMENT;
+    if (p->max_candidates > kNmsStaticMaxK) {
+        tk_error_set_detail("nms (static scratch): max_candidates %u is above the %u this entry point holds scratch for; "
+                            "use tk_kernels_nms_classwise", p->max_candidates, kNmsStaticMaxK);
+        return TK_ERROR_BUFFER_TOO_SMALL;
+    }
+    if (p->num_frames == 0) return TK_SUCCESS;
+    NmsK k{};
+    k.cands = p->d_candidates; k.counts = p->d_counts; k.dets = p->d_detections; k.num_dets = p->d_num_detections;
+    k.cap = p->max_candidates; k.max_det = p->max_detections;
+    k.Kp = 512; while (k.Kp < k.cap) k.Kp <<= 1;    // >= 512: the register sort exchanges through 512-entry buffers
+    k.thr = p->iou_threshold; k.agnostic = p->class_agnostic;
+    const bool any_restore = p->restore_src_width || p->restore_src_height || p->restore_in_width || p->restore_in_height;
+    if (any_restore) {
+        if (!p->restore_src_width || !p->restore_src_height || !p->restore_in_width || !p->restore_in_height)
+            return TK_ERROR_INVALID_DIMENSIONS;
+        k.restore = 1;
+        k.sx = (float)p->restore_src_width / (float)p->restore_in_width;
+        k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
+    }
+    k.num_frames = p->num_frames;
+    uint8_t* scratch = nullptr;
+    const tk_error_code_t rc = nms_static_scratch(&scratch);
+    if (rc != TK_SUCCESS) return rc;
+    const uint32_t pitch = k.Kp;                                               // one work area = nms_smem_bytes(pitch)
+    const size_t areas = kNmsStaticBytes / nms_smem_bytes(pitch);              // 8 at 16384 candidates ... 256 at 512
+    const uint32_t grid = p->num_frames < areas ? p->num_frames : (uint32_t)areas;
+    nms_global_kernel<<<grid, kNmsThreads, 0, stream>>>(k, scratch, pitch);
+    return launch_status("nms_global_kernel (static scratch)");
 }

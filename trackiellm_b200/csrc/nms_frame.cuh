@@ -39,7 +39,7 @@ __device__ __forceinline__ float iou_rect(int4 a, int4 b) {
 }
 
 // Work area: keys u64, box int4, pos u32, cls u32, dead u8, keys2 u64, segmask u64 per entry + one kept bit per entry.
-__host__ __device__ inline size_t nms_smem_bytes(uint32_t Kp) { return (size_t)Kp * (8 + 16 + 4 + 4 + 1 + 8 + 8) + Kp / 8; }
+__host__ __device__ constexpr size_t nms_smem_bytes(uint32_t Kp) { return (size_t)Kp * (8 + 16 + 4 + 4 + 1 + 8 + 8) + Kp / 8; }
 
 // Bitonic sort of Kp 64-bit keys in shared memory (ascending), optional u32 payload.
 template <int THREADS, bool PAYLOAD>

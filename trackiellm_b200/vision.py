@@ -142,6 +142,26 @@ def nms_classwise(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float
     return detections, num_detections
 
 
+def nms_classwise_static(candidates: torch.Tensor, counts: torch.Tensor, iou_thr: float, detections: torch.Tensor,
+                         num_detections: torch.Tensor, *, class_agnostic: bool = False,
+                         restore: tuple[int, int, int, int] | None = None) -> None:
+    """tk_b200_nms_classwise_static: tk_kernels_nms_classwise with its scratch in a static device array — the library
+    allocates nothing, and neither does this wrapper: the caller passes the outputs (detections int32
+    [N,max_detections,7], num_detections int32 [N]).  At most nms_static_max_candidates() candidates per frame; calls
+    that overlap on the GPU race (they share the array)."""
+    _require_cuda(candidates, "candidates")
+    n, cap = candidates.shape[0], candidates.shape[1]
+    prm = capi.NmsParams(candidates.data_ptr(), counts.data_ptr(), n, cap, iou_thr, detections.shape[1],
+                         int(class_agnostic), detections.data_ptr(), num_detections.data_ptr(),
+                         *(restore or (0, 0, 0, 0)))
+    with torch.cuda.device(candidates.device):
+        capi.check(capi.lib().tk_b200_nms_classwise_static(C.byref(prm), _stream()), "tk_b200_nms_classwise_static")
+
+
+def nms_static_max_candidates() -> int:
+    return int(capi.lib().tk_b200_nms_classwise_static_max_candidates())
+
+
 def postprocess_fused(logits: torch.Tensor, conf_thr: float, iou_thr: float, max_detections: int, *, act: int = ACT_RAW,
                       max_candidates: int = 4096, class_agnostic: bool = False,
                       restore: tuple[int, int, int, int] | None = None, layout: int = 0):
