@@ -57,6 +57,13 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
     float* ebuf = reinterpret_cast<float*>(wpre + k.nwords);       // softmax only: [warps][C]
     __shared__ uint32_t cta_tot[kDecCluster];                      // filled by every CTA of the cluster
     __shared__ uint32_t stage[kDecStage * 7];                      // this CTA's first kDecStage records, in row order
+    __shared__ unsigned long long tstamp[6];                       // debug trace: start, pass 1, prefix, expand, pass 2, end
+#ifdef TK_B200_TRACE_POST
+    const bool tr = k.trace.buf != nullptr && threadIdx.x == 0;
+#else
+    constexpr bool tr = false;                                     // phase stamps: `make trace` builds only
+#endif
+    if (tr) tstamp[0] = gtimer();
 
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t rank = cluster.block_rank();
@@ -102,6 +109,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
         }
     }
     __syncthreads();
+    if (tr) tstamp[1] = gtimer();
     asm volatile("barrier.cluster.wait.aligned;" ::: "memory");             // every peer CTA has started
 
     // ---- exclusive prefix over the bitmap words; totals to every peer through DSMEM ----
@@ -123,6 +131,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
             *cluster.map_shared_rank(&cta_tot[rank], lane) = run;  // DSMEM store into every peer
     }
     __syncthreads();
+    if (tr) tstamp[2] = gtimer();
     // The frame-level offset is only needed to write the records out: arrive now, wait after
     // the rows are decoded, so the cluster exchange hides behind pass 2.
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
@@ -143,6 +152,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
         }
     }
     __syncthreads();
+    if (tr) tstamp[3] = gtimer();
     auto row_of = [&](uint32_t sidx) -> uint32_t { return stage[sidx * 7]; };
     auto put = [&](uint32_t sidx, const tk_b200_candidate_t& c) {
         if (lane == 0) {
@@ -161,6 +171,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
         put(sidx, decode_row<ACT>(k, fl + (size_t)r * k.L, r, lane, my_e, q));
     }
     __syncthreads();
+    if (tr) tstamp[4] = gtimer();
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     uint32_t frame_pre = 0, frame_tot = 0;
 #pragma unroll
@@ -200,6 +211,10 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
             }
         }
     }
+#ifdef TK_B200_TRACE_POST
+    if (k.trace.buf) __syncthreads();                              // the end stamp covers every thread's writes
+#endif
+    if (tr) { tstamp[5] = gtimer(); trace_put(k.trace, 3u, blockIdx.x, local_tot, tstamp, 6); }
     if constexpr (NMS) {
         // Every CTA of the cluster has written its slice of the frame's list (rank 0 also the count): release them to
         // the first CTA, which goes on to the NMS; the others are done.
@@ -219,6 +234,8 @@ static tk_error_code_t launch_decode(const DecK& k, const NmsTail* tail, uint32_
     const NmsTail t = tail ? *tail : NmsTail{};
     if (smem > 48 * 1024)
         TK_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), TK_ERROR_GPU_CUDA_ERROR);
+    // (The largest shared-memory carve-out, which would spare the SMs a reconfiguration after the pre-process kernel, was
+    // measured: decode_kernel 42.3 -> 59.4 us.  The kernel wants its L1.)
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(frames * kDecCluster);
     cfg.blockDim = dim3(kDecThreads);
@@ -251,6 +268,7 @@ static tk_error_code_t decode_launch_common(const tk_b200_decode_params_t* p, co
     k.nwords = k.rows_per_cta / 32;
     k.cap = p->max_candidates;
     k.thr = p->confidence_threshold;
+    k.trace = trace_target();
     size_t smem = (size_t)k.nwords * 8 + (p->activation == TK_B200_ACT_SOFTMAX ? (size_t)kDecWarps * k.C * 4 : 0);
     if (tail && smem < nms_smem_bytes(kNmsSmall)) smem = nms_smem_bytes(kNmsSmall);   // the NMS phase overlays the decode buffers
     if (smem > (size_t)dev->max_smem_optin - 1024 - 8192) {

@@ -22,6 +22,7 @@ struct DecK {
     uint32_t nwords;           // rows_per_cta / 32
     uint32_t cap;
     float thr;
+    TraceBuf trace;            // debug: per-CTA phase stamps (tk_b200_debug_trace), buf == nullptr when off
 };
 
 template <int ACT>

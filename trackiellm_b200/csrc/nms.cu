@@ -84,6 +84,7 @@ extern "C" tk_error_code_t tk_kernels_nms_classwise(const tk_b200_nms_params_t* 
         k.sy = (float)p->restore_src_height / (float)p->restore_in_height;
     }
     k.num_frames = p->num_frames;
+    k.trace = trace_target();
     if (p->max_candidates > kNmsMaxK) {
         // above the shared-memory layout: global work areas from the stream-ordered allocator, one per CTA
         uint32_t pitch = 2 * kNmsMaxK;

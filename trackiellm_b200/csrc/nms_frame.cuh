@@ -20,6 +20,7 @@ struct NmsK {
     float sx, sy;                   // src/in scale of the optional coordinate restore
     uint32_t num_frames;
     uint32_t select;                // 0: every frame; 1: only frames of <= kNmsSmall candidates; 2: only the others
+    TraceBuf trace;                 // debug: per-frame phase stamps (tk_b200_debug_trace), buf == nullptr when off
 };
 
 static constexpr uint32_t kNmsSmall = 512;   // the register path's limit: 25 KB of shared memory per CTA instead of 200 KB
@@ -104,8 +105,15 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     __shared__ unsigned long long blk_kept;
     __shared__ uint32_t warp_tot[kNmsWarps];
     __shared__ uint32_t seg_overflow;
+    __shared__ unsigned long long tstamp[6];                       // debug trace: start, sorts, segment scan, pair masks, resolve, end
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef TK_B200_TRACE_POST
+    const bool tr = k.trace.buf != nullptr && tid == 0;
+#else
+    constexpr bool tr = false;                                     // phase stamps: `make trace` builds only
+#endif
+    if (tr) tstamp[0] = gtimer();
     const tk_b200_candidate_t* in = k.cands + (size_t)frame * k.cap;
     tk_b200_candidate_t* out = k.dets + (size_t)frame * k.max_det;
     const uint32_t K = min(k.counts[frame], k.cap);
@@ -186,6 +194,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     bitonic_sort<THREADS, false>(keys2, nullptr, Kp, tid);
     }
 
+    if (tr) tstamp[1] = gtimer();
     // ---- A. per-candidate suppressor mask inside its class segment -----------------
     // Suppression never crosses classes.  For the candidate at class-order position t
     // with R same-class predecessors, bit r of segmask[t] <=> the predecessor of
@@ -243,6 +252,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
     __syncthreads();
 
     uint32_t run = 0;
+    if (tr) tstamp[2] = gtimer();
     if (!seg_overflow) {
         const uint32_t total = wpre[K];
         const uint32_t per = (total + THREADS - 1) / THREADS;
@@ -272,6 +282,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
             if (m) atomicOr(&segmask[t], m);
         }
         __syncthreads();
+        if (tr) tstamp[3] = gtimer();
         // ---- B. each segment head resolves its segment sequentially (<= 64 steps).  Keys and masks
         //         come in groups of four independent loads, so the chain per element is the kept-mask
         //         update alone, not a shared-memory round trip ----
@@ -303,6 +314,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
             }
         }
         __syncthreads();
+        if (tr) tstamp[4] = gtimer();
         // ---- C. kept bitmap -> ordered compaction in score order ---------------------
         for (uint32_t base = 0; base < K; base += THREADS) {
             const uint32_t i = base + tid;
@@ -329,6 +341,7 @@ __device__ __forceinline__ void nms_frame(const NmsK& k, const uint32_t frame, u
             if (run >= k.max_det) break;
         }
         if (tid == 0) k.num_dets[frame] = min(run, k.max_det);
+        if (tr) { tstamp[5] = gtimer(); trace_put(k.trace, 4u, frame, K, tstamp, 6); }
         return;
     }
 
