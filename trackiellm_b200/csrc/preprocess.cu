@@ -615,6 +615,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         }
     };
 
+    uint32_t ready_seen = 0;                     // records known to be published (acquire-loaded from rec_ready)
     // Row set-up: publish the row number, take the record, wait for the two source rows.
     struct Row { const uint8_t* row0; const uint8_t* row1; uint8_t* out; float yd, omy; bool vin;
 #ifdef TK_B200_CHECKED
@@ -623,9 +624,11 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     };
     auto begin_row = [&](uint32_t n, Row& r) {
         __syncwarp();                            // all lanes are done reading the rows being released
-        if (lane == 0) { __threadfence_block(); progress[tid >> 5] = n; }
-        while (*rec_ready <= n) __nanosleep(32);
-        __threadfence_block();
+        if (lane == 0) sts_release(&progress[tid >> 5], n);
+        // the producer runs up to kRecs records ahead: most rows find their record published by an earlier look
+        if (n >= ready_seen) {
+            while ((ready_seen = lds_acquire(rec_ready)) <= n) __nanosleep(32);
+        }
         const uint32_t e = n & (kRecs - 1);
         const uint4 ra = recs[2 * e], rb = recs[2 * e + 1];
         r.vin = !LBOX || (ra.w & 1u);

@@ -180,6 +180,15 @@ __device__ __forceinline__ void mbar_wait_backoff_addr(uint32_t addr, uint32_t p
         __nanosleep(64);
     }
 }
+// CTA-scope acquire load / release store on shared memory (flag hand-over between warps without a separate fence).
+__device__ __forceinline__ uint32_t lds_acquire(const volatile uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(const_cast<const uint32_t*>(p))) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_release(volatile uint32_t* p, uint32_t v) {
+    asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(smem_u32(const_cast<uint32_t*>(p))), "r"(v) : "memory");
+}
 // TMA 1-D bulk copy global -> shared, completion signalled on an mbarrier.
 // dst, src 16-byte aligned, bytes a multiple of 16.
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
