@@ -23,7 +23,12 @@ buf = torch.zeros((cap + 1) * 8, dtype=torch.int64, device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 
+FUSED = len(sys.argv) > 1 and sys.argv[1] == "fused"     # tk_kernels_postprocess_fused layout 0: one kernel, NMS in the cluster's first CTA
+
+
 def two():
+    if FUSED:
+        return V.postprocess_fused(logits, 0.5, 0.5, 500, layout=0)
     c, n = V.decode_detections(logits, 0.5)
     return V.nms_classwise(c, n, 0.5, 500)
 
@@ -37,9 +42,13 @@ for rep in range(3):
     lib.tk_b200_debug_trace(C.c_void_p(buf.data_ptr()), C.c_size_t(buf.numel() * 8))
     e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
     e0.record()
-    c, n = V.decode_detections(logits, 0.5)
-    e1.record()
-    V.nms_classwise(c, n, 0.5, 500)
+    if FUSED:
+        V.postprocess_fused(logits, 0.5, 0.5, 500, layout=0)
+        e1.record()
+    else:
+        c, n = V.decode_detections(logits, 0.5)
+        e1.record()
+        V.nms_classwise(c, n, 0.5, 500)
     e2.record()
     torch.cuda.synchronize()
     lib.tk_b200_debug_trace(None, 0)
@@ -55,7 +64,7 @@ for rep in range(3):
         if not m.any():
             continue
         tk = t[m]
-        t0 = tk[:, 0].min()
+        t0 = t[kid == 3][:, 0].min() if FUSED else tk[:, 0].min()     # fused: NMS stamps on the decode CTAs' clock
         rel = (tk - t0) / 1e3
         print(f"{name}: {m.sum()}  start {rel[:, 0].min():.1f}..{rel[:, 0].max():.1f} us, end {rel[:, 5].min():.1f}..{rel[:, 5].max():.1f} us (median {np.median(rel[:, 5]):.1f})")
         ph = np.diff(rel, axis=1)

@@ -45,17 +45,22 @@ struct NmsTail {
 
 // 4 CTAs per SM (<= 32 registers): with 3, only 48 of the 64 clusters of the bench batch are
 // co-resident (a cluster of 8 must sit in one GPC) and the launch needs two waves.
+// The form with the NMS tail: clusters of 4 and 3 CTAs per SM (<= 42 registers, which nms_frame's 40 fit without the
+// spills it has at 32): 64 frames x 4 = 256 CTAs are still one wave.
+static constexpr int kDecClusterNms = 4;
+
 template <int ACT, bool PACKED, bool NMS>
-__global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, const NmsTail tail) {
+__global__ void __launch_bounds__(kDecThreads, NMS ? 3 : 4) decode_kernel(const DecK k, const NmsTail tail) {
+    constexpr int CL = NMS ? kDecClusterNms : kDecCluster;
     // Possibly launched under the tail of the pipeline's pre-process kernel (pdl_chain_hint): nothing is read or written
-    // before that grid has completed.  A no-op for a plain launch.  Then let nms_kernel, which starts the same way, in.
+    // before that grid has completed.  A no-op for a plain launch.  nms_kernel, which starts the same way, is let in
+    // when this CTA has written its records (end of the kernel): its launch then overlaps this grid's drain.
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     extern __shared__ __align__(16) uint8_t dsm[];
     uint32_t* flags = reinterpret_cast<uint32_t*>(dsm);            // [nwords] ballot bitmap
     uint32_t* wpre = flags + k.nwords;                             // [nwords] exclusive prefix of popc
     float* ebuf = reinterpret_cast<float*>(wpre + k.nwords);       // softmax only: [warps][C]
-    __shared__ uint32_t cta_tot[kDecCluster];                      // filled by every CTA of the cluster
+    __shared__ uint32_t cta_tot[CL];                               // filled by every CTA of the cluster
     __shared__ uint32_t stage[kDecStage * 7];                      // this CTA's first kDecStage records, in row order
     __shared__ unsigned long long tstamp[6];                       // debug trace: start, pass 1, prefix, expand, pass 2, end
 #ifdef TK_B200_TRACE_POST
@@ -67,7 +72,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
 
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t rank = cluster.block_rank();
-    const uint32_t frame = blockIdx.x / kDecCluster;
+    const uint32_t frame = blockIdx.x / CL;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float* fl = k.logits + (size_t)frame * k.P * k.L;
     const uint32_t row0 = rank * k.rows_per_cta;
@@ -127,7 +132,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
             if (w < k.nwords) wpre[w] = run + inc - c;
             run += __shfl_sync(0xffffffffu, inc, 31);
         }
-        if (lane < kDecCluster)
+        if (lane < CL)
             *cluster.map_shared_rank(&cta_tot[rank], lane) = run;  // DSMEM store into every peer
     }
     __syncthreads();
@@ -175,7 +180,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     uint32_t frame_pre = 0, frame_tot = 0;
 #pragma unroll
-    for (int r = 0; r < kDecCluster; ++r) {
+    for (int r = 0; r < CL; ++r) {
         uint32_t t = cta_tot[r];
         frame_pre += (uint32_t)r < rank ? t : 0u;
         frame_tot += t;
@@ -215,6 +220,7 @@ __global__ void __launch_bounds__(kDecThreads, 4) decode_kernel(const DecK k, co
     if (k.trace.buf) __syncthreads();                              // the end stamp covers every thread's writes
 #endif
     if (tr) { tstamp[5] = gtimer(); trace_put(k.trace, 3u, blockIdx.x, local_tot, tstamp, 6); }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if constexpr (NMS) {
         // Every CTA of the cluster has written its slice of the frame's list (rank 0 also the count): release them to
         // the first CTA, which goes on to the NMS; the others are done.
@@ -237,13 +243,14 @@ static tk_error_code_t launch_decode(const DecK& k, const NmsTail* tail, uint32_
     // (The largest shared-memory carve-out, which would spare the SMs a reconfiguration after the pre-process kernel, was
     // measured: decode_kernel 42.3 -> 59.4 us.  The kernel wants its L1.)
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(frames * kDecCluster);
+    const int cl = tail ? kDecClusterNms : kDecCluster;
+    cfg.gridDim = dim3(frames * cl);
     cfg.blockDim = dim3(kDecThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = kDecCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl_chain_hint() ? 2 : 1;
@@ -263,7 +270,8 @@ static tk_error_code_t decode_launch_common(const tk_b200_decode_params_t* p, co
     k.logits = p->d_logits; k.obj = d_objectness; k.cands = p->d_candidates; k.counts = p->d_counts;
     k.bitmap = d_bitmap; k.nwf = (p->num_proposals + 31) / 32;
     k.P = p->num_proposals; k.C = p->num_classes; k.L = 5 + p->num_classes;
-    uint32_t per = (k.P + kDecCluster - 1) / kDecCluster;
+    const uint32_t cl = tail ? kDecClusterNms : kDecCluster;
+    uint32_t per = (k.P + cl - 1) / cl;
     k.rows_per_cta = (per + 31) & ~31u;
     k.nwords = k.rows_per_cta / 32;
     k.cap = p->max_candidates;

@@ -5,7 +5,10 @@
 
 namespace tkb {
 
-static constexpr int kDecCluster = 8;
+#ifndef TK_DEC_CLUSTER
+#define TK_DEC_CLUSTER 8
+#endif
+static constexpr int kDecCluster = TK_DEC_CLUSTER;    // CTAs per frame in decode_kernel (experiment builds override it)
 static constexpr int kDecThreads = 512;
 static constexpr int kDecWarps = kDecThreads / 32;
 

@@ -357,9 +357,10 @@ static tk_error_code_t run_kernels(tk_b200_pipeline_t* p, const void* d_frames, 
         d.d_candidates = d_cands; d.d_counts = d_counts; d.max_candidates = c.max_candidates;
     }
     // pre-process -> decode -> NMS as a programmatic-dependent-launch chain (tk_common.cuh, pdl_chain_hint): OFF unless
-    // TK_B200_PDL_CHAIN=1.  Measured (profiles/r2_experiments.md §8): 182.8 us per 64-frame step against 164.8 us — the
-    // decode clusters that become resident under the pre-process kernel's tail only wait there, and the SM resources
-    // they hold slow the pre-process CTAs that are still working.  Only process_device (pdl_pre), three-kernel form.
+    // TK_B200_PDL_CHAIN=1.  Measured twice (profiles/r2_experiments.md §7, §12): with the dependents announced at the top
+    // of each kernel 182.8 us per 64-frame step against 164.8 us — the decode clusters that become resident under the
+    // pre-process kernel's tail only wait there, and what they hold slows the CTAs still working; announced at the END of
+    // each kernel (the form in the tree) 157.7 us against 149.4 us.  Only process_device (pdl_pre), three-kernel form.
     static const bool chain_env = [] { const char* e = getenv("TK_B200_PDL_CHAIN"); return e && atoi(e) != 0; }();
     struct HintGuard { bool& h; bool old; HintGuard(bool& r, bool v) : h(r), old(r) { h = v; } ~HintGuard() { h = old; } }
         hint(pdl_chain_hint(), chain_env && pdl_pre && d_frames && d_logits && !post_done && mode == 0);
