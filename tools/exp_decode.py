@@ -6,7 +6,7 @@ import bench
 from trackiellm_b200 import _capi as capi, vision as V
 
 B = 64
-fr, lg = bench.make_inputs(8, 0)
+fr, lg = bench.make_inputs(bench.WORKLOADS["1080p-rgb"], 8, 0)
 import numpy as np
 fr = np.concatenate([fr] * 8); lg = np.concatenate([lg] * 8)
 df, dl = torch.from_numpy(fr).cuda(), torch.from_numpy(lg).cuda()

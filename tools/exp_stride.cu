@@ -42,8 +42,24 @@ void run(const float* x, size_t rows, int L, unsigned* out, const char* name) {
     printf("%-44s L=%d: %7.1f us  -> %6.1f B/row at 6.5 TB/s-equivalent, %6.1f Mrows/s  (%s)\n", name, L, us, us * 6.5e6 / rows, rows / us,
            cudaGetErrorString(cudaGetLastError()));
 }
-int main() {
+int main(int argc, char** argv) {
     const size_t rows = 64ull * 25200;
+    if (argc > 1) {      // ./exp_stride limit: the plain and the hinted loads under each cudaLimitMaxL2FetchGranularity
+        for (size_t g : {32, 64, 128}) {
+            cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, g);
+            size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+            printf("--- cudaLimitMaxL2FetchGranularity = %zu (%s; in effect %zu)\n", g, cudaGetErrorString(e), got);
+            float* x; unsigned* out;
+            cudaMalloc(&x, rows * 85 * 4 + 1024); cudaMalloc(&out, 4);
+            cudaMemset(x, 0, rows * 85 * 4);
+            run<0>(x, rows, 85, out, "__ldg (ld.global.nc)");
+            run<6>(x, rows, 85, out, "ld.global.nc.L1::no_allocate");
+            run<7>(x, rows, 85, out, "ld.global.nc.L1::no_allocate.L2::64B");
+            run<1>(x, rows, 85, out, "ld.global.cg");
+            cudaFree(x); cudaFree(out);
+        }
+        return 0;
+    }
     for (int L : {85, 96}) {
         float* x; unsigned* out;
         cudaMalloc(&x, rows * L * 4 + 1024); cudaMalloc(&out, 4);
