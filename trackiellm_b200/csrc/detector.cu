@@ -14,6 +14,8 @@
 // third-party engine outside this path; without a bound network detect()
 // fails with TK_ERROR_INFERENCE_FAILED — there is no CPU fallback.
 #include "tk_common.cuh"
+#include <stdlib.h>
+#include <time.h>
 
 #include <stdlib.h>
 #include <string.h>
@@ -180,7 +182,7 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
     if ((rc = reserve(d, 1, tensor_bytes)) != TK_SUCCESS) return rc;
     if ((rc = reserve(d, 2, logit_bytes)) != TK_SUCCESS) return rc;
     if ((rc = reserve(d, 3, off_cnt + 8 * (size_t)n + 256)) != TK_SUCCESS) return rc;
-    if ((rc = reserve_pinned(d, det_bytes + 8 * (size_t)n)) != TK_SUCCESS) return rc;
+    if ((rc = reserve_pinned(d, off_cnt - off_det + 8 * (size_t)n)) != TK_SUCCESS) return rc;
 
     uint8_t* d_frames = static_cast<uint8_t*>(d->d_buf[0]);
     float* d_tensor = static_cast<float*>(d->d_buf[1]);
@@ -191,9 +193,21 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
     uint32_t* d_cnt = reinterpret_cast<uint32_t*>(base + off_cnt);     // [n] candidates, then [n] detections
     cudaStream_t st = d->stream;
 
+    // TK_B200_DETECT_TRACE=1 (debug): synchronise after every phase and print where a call's time goes
+    static const bool ptrace = [] { const char* e = getenv("TK_B200_DETECT_TRACE"); return e && atoi(e) != 0; }();
+    static int ptrace_calls = 0;
+    double pt[8] = {}; int pi = 0;
+    auto mark = [&](bool sync) {
+        if (!ptrace) return;
+        if (sync) cudaStreamSynchronize(st);
+        timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+        if (pi < 8) pt[pi++] = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+    };
+    mark(false);
     // preprocess_frame, :223-259 (upload + kernel; constants of :248-249)
     for (uint32_t i = 0; i < n; ++i)
         TK_CUDA_TRY(cudaMemcpyAsync(d_frames + pitch * i, frames[i].data, fbytes, cudaMemcpyHostToDevice, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    mark(true);
     tk_b200_preprocess_batch_params_t pp{};
     pp.d_input = d_frames; pp.input_frame_pitch_bytes = pitch; pp.num_frames = n;
     pp.input_width = f0.width; pp.input_height = f0.height; pp.input_stride_bytes = stride; pp.input_format = f0.format;
@@ -202,6 +216,7 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
     pp.mean = TkFloat3{0.485f, 0.456f, 0.406f};
     pp.std_dev = TkFloat3{0.229f, 0.224f, 0.225f};
     if ((rc = tk_b200_preprocess_batch(&pp, st)) != TK_SUCCESS) return rc;
+    mark(true);
 
     // run_inference, :261-301 — the bound network, device pointers in and out
     const tk_error_code_t irc = d->infer(d->infer_user, d_tensor, n, W, H, d_logits, P, L, st);
@@ -211,33 +226,41 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
         return TK_ERROR_INFERENCE_FAILED;
     }
 
+    mark(true);
     // postprocess_detections, :303-368
     tk_b200_decode_params_t dp{};
     dp.d_logits = d_logits; dp.num_frames = n; dp.num_proposals = P; dp.num_classes = C;
     dp.confidence_threshold = d->config.confidence_threshold; dp.activation = d->activation;
     dp.d_candidates = d_c; dp.d_counts = d_cnt; dp.max_candidates = kDetCap;
     if ((rc = tk_kernels_decode_detections(&dp, st)) != TK_SUCCESS) return rc;
+    mark(true);
     tk_b200_nms_params_t np{};
     np.d_candidates = d_c; np.d_counts = d_cnt; np.num_frames = n; np.max_candidates = kDetCap;
     np.iou_threshold = d->config.iou_threshold; np.max_detections = kDetMax; np.class_agnostic = 0;
     np.d_detections = d_d; np.d_num_detections = d_cnt + n;
     np.restore_src_width = f0.width; np.restore_src_height = f0.height; np.restore_in_width = W; np.restore_in_height = H;   // :365
     if ((rc = tk_kernels_nms_classwise(&np, st)) != TK_SUCCESS) return rc;
+    mark(true);
 
-    uint32_t* h_cnt = reinterpret_cast<uint32_t*>(d->h_pinned + det_bytes);       // [n] detections, then [n] candidates
+    // detections and both count arrays are contiguous on the device (off_det .. off_cnt + 8 n): ONE copy brings them back
+    const size_t back_bytes = off_cnt - off_det + 8 * (size_t)n;
     tk_b200_candidate_t* h_det = reinterpret_cast<tk_b200_candidate_t*>(d->h_pinned);
-    TK_CUDA_TRY(cudaMemcpyAsync(h_cnt, d_cnt + n, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
-    TK_CUDA_TRY(cudaMemcpyAsync(h_cnt + n, d_cnt, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
-    TK_CUDA_TRY(cudaMemcpyAsync(h_det, d_d, det_bytes, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+    const uint32_t* h_ncand = reinterpret_cast<const uint32_t*>(d->h_pinned + (off_cnt - off_det));   // [n] candidates
+    uint32_t* h_ndet = reinterpret_cast<uint32_t*>(d->h_pinned + (off_cnt - off_det)) + n;           // [n] detections
+    TK_CUDA_TRY(cudaMemcpyAsync(d->h_pinned, base + off_det, back_bytes, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
     if (cudaStreamSynchronize(st) != cudaSuccess) {
         tk_error_set_detail("detect: %s", cudaGetErrorString(cudaGetLastError()));
         return TK_ERROR_INFERENCE_FAILED;
     }
+    mark(false);
+    if (ptrace && ++ptrace_calls % 50 == 0)
+        fprintf(stderr, "detect trace (us, phases serialised): upload %.1f  pre-process %.1f  network %.1f  decode %.1f  nms %.1f  download+sync %.1f\n",
+                pt[1] - pt[0], pt[2] - pt[1], pt[3] - pt[2], pt[4] - pt[3], pt[5] - pt[4], pt[6] - pt[5]);
     // The reference keeps every row that passes the threshold (:339-355); the kernels above cap a frame at kDetCap
     // candidates.  A frame that went over (a low threshold, a crowd) is done again without a cap — never truncated.
     bool redone = false;
     for (uint32_t i = 0; i < n; ++i) {
-        if (h_cnt[n + i] <= kDetCap) continue;
+        if (h_ncand[i] <= kDetCap) continue;
         const uint32_t restore[4] = {f0.width, f0.height, W, H};
         if ((rc = postprocess_frame_uncapped(d_logits + (size_t)i * P * L, P, C, d->activation, d->config.confidence_threshold,
                                              d->config.iou_threshold, kDetMax, 0, restore, d_d + (size_t)i * kDetMax,
@@ -245,7 +268,7 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
             cudaStreamSynchronize(st);
             return rc;
         }
-        TK_CUDA_TRY(cudaMemcpyAsync(h_cnt + i, d_cnt + n + i, 4, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
+        TK_CUDA_TRY(cudaMemcpyAsync(h_ndet + i, d_cnt + n + i, 4, cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
         TK_CUDA_TRY(cudaMemcpyAsync(h_det + (size_t)i * kDetMax, d_d + (size_t)i * kDetMax, kDetMax * sizeof(tk_b200_candidate_t),
                                     cudaMemcpyDeviceToHost, st), TK_ERROR_GPU_MEMORY_COPY_FAILED);
         redone = true;
@@ -257,7 +280,7 @@ extern "C" tk_error_code_t tk_b200_object_detector_detect_batch(tk_object_detect
 
     // results array, :359-361 (label points into the caller's table, tk_object_detector.h:50-52)
     for (uint32_t i = 0; i < n; ++i) {
-        const uint32_t k = h_cnt[i] < kDetMax ? h_cnt[i] : kDetMax;
+        const uint32_t k = h_ndet[i] < kDetMax ? h_ndet[i] : kDetMax;
         if (k == 0) continue;
         tk_detection_result_t* res = static_cast<tk_detection_result_t*>(calloc(k, sizeof(tk_detection_result_t)));
         if (!res) {
