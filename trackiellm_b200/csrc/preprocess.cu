@@ -28,6 +28,10 @@
 //     Markstein fma sequence on a host-computed correctly rounded reciprocal.
 #include "decode_row.cuh"
 
+#include <atomic>
+#include <stdio.h>
+#include <stdlib.h>
+
 namespace tkb {
 
 enum { FMT_RGB8 = 0, FMT_RGBA8 = 1, FMT_I420 = 2 };
@@ -76,7 +80,18 @@ struct PreK {
     unsigned long long cplane[3];   // byte offset of the tensor plane that SOURCE channel c is written to (BGR: 2 - c)
     TraceBuf trace;         // debug: per-CTA record (tk_b200_debug_trace), buf == nullptr when off
     ScanK scan;
+    // Work distribution: global output rows [0, static_rows) are cut into one contiguous run per CTA; the rest,
+    // [static_rows, N * dst_h), is handed out in chunks of dyn_rows rows from an atomic counter (g_pre_work[dyn_slot]) to
+    // whichever CTA is through its run — CTAs of one launch differ by up to 45 % in speed (profiles/r2_experiments.md §15).
+    unsigned long long static_rows;
+    uint32_t dyn_rows, dyn_chunks, dyn_slot;
 };
+
+// Chunk counters of the launches in flight (a launch takes the next slot; the last CTA to finish clears its slot's two
+// words, so every launch finds zeros) — file-scope device memory: no workspace in the C-ABI, no memset on the stream.
+static constexpr uint32_t kPreSlots = 64;
+static __device__ unsigned int g_pre_work[kPreSlots];
+static __device__ unsigned int g_pre_done[kPreSlots];
 
 static constexpr float kBias = 8388608.0f;   // 2^23: 0x4B0000bb == 2^23 + bb
 
@@ -332,7 +347,8 @@ static constexpr uint32_t kRecs = 32;
 static constexpr uint32_t kSmemRecs = 512;                        // 32 x 32 B
 static constexpr uint32_t kSmemQ0 = kSmemRecs + kRecs * 32;       // [kRecs] u32: first ring sequence number row n needs (producer only)
 static constexpr uint32_t kSmemChk = kSmemQ0 + kRecs * 4;         // CHECKED build: [kRecs] {frame, source row, n}
-static constexpr uint32_t kSmemTabs = 2048;                       // column tables
+static constexpr uint32_t kSmemRq = 2048;                         // [8] {first, end} global output rows of the work ranges in flight (producer only)
+static constexpr uint32_t kSmemTabs = 2176;                       // column tables
 
 // Block: tx * ty consumer threads (320 at a 640-pixel row) + the producer warp (+ the scanner warp, see ScanK).
 // (512-thread CTAs — three row groups at <= 64 registers, 32 resident warps per SM instead of 22 — were built and
@@ -417,13 +433,12 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         return;
     }
 
-    // This CTA's contiguous run of global output rows.
+    // This CTA's contiguous run of the statically distributed output rows (the rest comes in chunks, see PreK).
     const unsigned long long total = (unsigned long long)p.num_frames * p.dst_h;
-    const unsigned long long g0 = total * blockIdx.x / gridDim.x;
-    const unsigned long long g1 = total * (blockIdx.x + 1) / gridDim.x;
-    if (g0 >= g1) { finish(); return; }
-    const uint32_t nrows_cta = (uint32_t)(g1 - g0);
+    const unsigned long long g0 = p.static_rows * blockIdx.x / gridDim.x;
+    const unsigned long long g1 = p.static_rows * (blockIdx.x + 1) / gridDim.x;
     constexpr uint32_t ESZ = F16 ? 2 : 4;
+    constexpr uint32_t kRecEnd = 8u;             // record flag: no more rows for this CTA
 
     // ======================= producer warp =======================================
     // Two cursors over the CTA's items (an item = the CTA's rows inside one frame): the ARMING cursor walks the source-row
@@ -432,43 +447,107 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     // releases is looked up here (q0s), so sequence arithmetic lives in this warp only.
     if (tid >= ncons) {                      // (the scanner warp, tid >= ncons + 32, left above)
         const uint32_t lane = tid - ncons;
-        const uint32_t f_first = (uint32_t)(g0 / p.dst_h), f_last = (uint32_t)((g1 - 1) / p.dst_h);
-        auto item_rows = [&](uint32_t f, uint32_t& h0, uint32_t& h1) {
-            h0 = (f == f_first) ? (uint32_t)(g0 - (unsigned long long)f_first * p.dst_h) : 0u;
-            unsigned long long end = g1 - (unsigned long long)f * p.dst_h;
-            h1 = end < p.dst_h ? (uint32_t)end : p.dst_h;
-        };
         auto frame_ptr = [&](uint32_t f) -> const uint8_t* {
             return p.in_ptrs ? p.in_ptrs[f] : p.in_base + (unsigned long long)f * p.frame_pitch;
         };
         const size_t plane = (size_t)p.dst_w * p.dst_h;
-        uint32_t fa = f_first, seq = 0, a_a = 0;                 // arming cursor: frame, sequences armed so far, first inside row
+        // Work ranges [first, end) of global output rows, in the order this CTA takes them: its static run, then chunks
+        // from the launch's counter.  The arming cursor fetches them; the record cursor, which lags it, reads them back
+        // from a queue of 8 (more than the ring can hold rows of).  An ITEM is the part of a range inside one frame.
+        unsigned long long* rq = reinterpret_cast<unsigned long long*>(smem + kSmemRq);
+        uint32_t nfetched = 0;                                   // ranges fetched so far
+        bool exhausted = false;                                  // the counter has run out (or there is no dynamic part)
+        auto fetch_range = [&](uint32_t ranges_done_by_records) -> bool {
+            if (exhausted || nfetched - ranges_done_by_records >= 8) return false;
+            unsigned long long ra_ = g0, rb_ = g1;
+            if (nfetched > 0) {
+                if (p.dyn_chunks == 0) { exhausted = true; return false; }
+                uint32_t c = 0;
+                if (lane == 0) c = atomicAdd(&g_pre_work[p.dyn_slot], 1u);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                if (c >= p.dyn_chunks) { exhausted = true; return false; }
+                ra_ = p.static_rows + (unsigned long long)c * p.dyn_rows;
+                rb_ = min(ra_ + p.dyn_rows, total);
+            }
+            if (lane == 0) { rq[2 * (nfetched & 7)] = ra_; rq[2 * (nfetched & 7) + 1] = rb_; }
+            __syncwarp();
+            ++nfetched;
+            return true;
+        };
+        // cursor over the ranges: (index of its range, next global row, end of the range)
+        uint32_t ia = 0, ir = 0;                                 // ranges the arming / record cursor has finished
+        unsigned long long ga = 0, gea = 0, gr = 0, ger = 0;     // current range of each cursor: next row, end
+        bool a_has = false, r_has = false;                       // cursor holds a range
+        uint32_t fa = 0, seq = 0, a_a = 0;                       // arming cursor: frame, sequences armed so far, first inside row
         int ra = 0, na = 0, ylo_a = 0;                           //   rows armed / to arm in the item, its first source row
         const uint8_t* base_a = nullptr;
         bool a_open = false, a_done = false;
-        uint32_t fr = f_first, hr = 0, h1r = 0, a_r = 0, b_r = 0, seqbase_r = 0, n_pub = 0;   // record cursor
+        uint32_t fr = 0, hr = 0, h1r = 0, a_r = 0, b_r = 0, seqbase_r = 0, n_pub = 0;   // record cursor
         int ylo_r = 0, nrows_r = 0;
-        bool r_open = false;
+        bool r_open = false, r_done = false;
 #ifdef TK_B200_CHECKED
         volatile uint32_t* chk = reinterpret_cast<volatile uint32_t*>(smem + kSmemChk);
 #endif
-        while (n_pub < nrows_cta) {                              // the last record needs the last source row: arming ends first
+        for (;;) {
+            // ---- open the next item of each cursor ----
             if (!a_open && !a_done) {
-                uint32_t h0, h1; item_rows(fa, h0, h1);
-                item_src_rows(p, h0, h1, ylo_a, na, a_a);
-                base_a = frame_ptr(fa); ra = 0; a_open = true;
+                if (a_has && ga == gea) { a_has = false; ++ia; }
+                if (!a_has) {
+                    if (ia < nfetched || fetch_range(ir)) { ga = rq[2 * (ia & 7)]; gea = rq[2 * (ia & 7) + 1]; a_has = true; }
+                    else if (exhausted) a_done = true;
+                }
+                if (a_has && ga < gea) {
+                    fa = (uint32_t)(ga / p.dst_h);
+                    const uint32_t h0 = (uint32_t)(ga - (unsigned long long)fa * p.dst_h);
+                    const uint32_t h1 = (uint32_t)min((unsigned long long)p.dst_h, h0 + (gea - ga));
+                    item_src_rows(p, h0, h1, ylo_a, na, a_a);
+                    base_a = frame_ptr(fa); ra = 0; a_open = true;
+                    ga += h1 - h0;
+                }
             }
-            if (!r_open) {
-                uint32_t h0, h1; item_rows(fr, h0, h1);
-                item_src_rows(p, h0, h1, ylo_r, nrows_r, a_r);
-                hr = h0; h1r = h1; b_r = min(h1, p.pad_top + p.new_h); r_open = true;
+            if (!r_open && !r_done) {
+                if (r_has && gr == ger) { r_has = false; ++ir; }
+                if (!r_has) {
+                    if (ir < nfetched) { gr = rq[2 * (ir & 7)]; ger = rq[2 * (ir & 7) + 1]; r_has = true; }
+                    else if (a_done) r_done = true;              // the arming cursor fetches first: nothing more will come
+                }
+                if (r_has && gr < ger) {
+                    fr = (uint32_t)(gr / p.dst_h);
+                    const uint32_t h0 = (uint32_t)(gr - (unsigned long long)fr * p.dst_h);
+                    const uint32_t h1 = (uint32_t)min((unsigned long long)p.dst_h, h0 + (ger - gr));
+                    item_src_rows(p, h0, h1, ylo_r, nrows_r, a_r);
+                    hr = h0; h1r = h1; b_r = min(h1, p.pad_top + p.new_h); r_open = true;
+                    gr += h1 - h0;
+                }
+            }
+            if (r_done) {
+                // every row has its record: one END record per row group, then this warp is done
+                const uint32_t min_n_ = __reduce_min_sync(0xffffffffu, progress[lane]);
+                if ((unsigned long long)n_pub + p.ty <= (unsigned long long)min_n_ + kRecs) {
+                    if (lane < p.ty) {
+                        const uint32_t e = (n_pub + lane) & (kRecs - 1);
+                        recs[2 * e] = make_uint4(p.ring_off, p.ring_off, 0u, kRecEnd);
+                        recs[2 * e + 1] = make_uint4(0u, 0u, 0u, 0u);
+                        q0s[e] = seqbase_r;
+#ifdef TK_B200_CHECKED
+                        chk[3 * e] = 0; chk[3 * e + 1] = 0; chk[3 * e + 2] = n_pub + lane;
+#endif
+                    }
+                    __syncwarp();
+                    if (lane == 0) { __threadfence_block(); *rec_ready = n_pub + p.ty; }
+                    break;
+                }
+                __nanosleep(64);
+                continue;
             }
             // lane j looks at output row hr + j of the record cursor's item
             const uint32_t h = hr + lane;
-            const bool in_item = h < h1r;
+            const bool in_item = r_open && h < h1r;
             const bool inside = in_item && h >= a_r && h < b_r;
             int y = 0; float yd = 0.0f;
-            uint32_t q0 = seqbase_r + (h >= b_r ? (uint32_t)nrows_r : 0u);   // padding: above the region nothing is released yet, below it everything
+            // padding: above the region nothing is released yet, below it everything; no item open: everything armed so far
+            // belongs to rows that are published (seqbase_r already counts the closed item)
+            uint32_t q0 = seqbase_r + ((r_open && h >= b_r) ? (uint32_t)nrows_r : 0u);
             if (inside) {
                 const float gy = __fmul_rn(p.y_ratio, (float)(h - p.pad_top));    // src/vision/tk_image_preprocessor.c:49,51,53
                 y = min(__float2int_rz(gy), (int)p.src_h - 2);
@@ -533,7 +612,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
                         seq += 1; ra += 1; did = true;
                     }
                 }
-                if (ra == na) { a_open = false; if (fa == f_last) a_done = true; else ++fa; }
+                if (ra == na) a_open = false;
             }
             // Publish the records of the leading rows whose two source rows are armed by now (a waiter tells barrier
             // phases apart by parity only, so it may look at full[slot] for sequence q only once q has been armed, which
@@ -564,10 +643,18 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
                 if (cnt) {
                     if (lane == 0) { __threadfence_block(); *rec_ready = n_pub + cnt; }
                     n_pub += cnt; hr += cnt; did = true;
-                    if (hr == h1r) { r_open = false; seqbase_r += (uint32_t)nrows_r; ++fr; }
+                    if (hr == h1r) { r_open = false; seqbase_r += (uint32_t)nrows_r; }
                 }
             }
             if (!did) __nanosleep(64);
+        }
+        if (p.dyn_chunks && lane == 0) {
+            // the last CTA of the launch to get here leaves the slot's counters at zero for the launch that takes it next
+            __threadfence();
+            if (atomicAdd(&g_pre_done[p.dyn_slot], 1u) == gridDim.x - 1) {
+                g_pre_work[p.dyn_slot] = 0u; g_pre_done[p.dyn_slot] = 0u;
+                __threadfence();
+            }
         }
         finish();
         return;
@@ -625,7 +712,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
 
     uint32_t ready_seen = 0;                     // records known to be published (acquire-loaded from rec_ready)
     // Row set-up: publish the row number, take the record, wait for the two source rows.
-    struct Row { const uint8_t* row0; const uint8_t* row1; uint8_t* out; float yd, omy; bool vin;
+    struct Row { const uint8_t* row0; const uint8_t* row1; uint8_t* out; float yd, omy; bool vin, end;
 #ifdef TK_B200_CHECKED
                  uint32_t chk_f; int chk_y;
 #endif
@@ -639,7 +726,8 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         }
         const uint32_t e = n & (kRecs - 1);
         const uint4 ra = recs[2 * e], rb = recs[2 * e + 1];
-        r.vin = !LBOX || (ra.w & 1u);
+        r.end = (ra.w & kRecEnd) != 0;           // no more rows for this CTA (the producer's last records)
+        r.vin = !r.end && (!LBOX || (ra.w & 1u));
         r.yd = __uint_as_float(ra.z); r.omy = __fsub_rn(1.0f, r.yd);
         r.row0 = smem + ra.x; r.row1 = smem + ra.y;
         r.out = reinterpret_cast<uint8_t*>(((unsigned long long)rb.w << 32) | rb.z);       // output row, tensor plane 0
@@ -761,20 +849,25 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
         }
     };
 
+    uint32_t rows_done = 0;
     if (Q <= p.tx) {
         // One quad per thread and row (rows of <= 640 pixels): its column constants stay in registers for the whole run —
         // two 16-byte table loads, six packed fp32 and a dozen ALU-pipe instructions less per row.
         Cols c{};
         const bool has = cx < Q;
         if (has) load_cols(cx, c);
-        for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+        for (uint32_t n = cy;; n += p.ty) {
             Row r; begin_row(n, r);
+            if (r.end) break;
             if (has) do_quad(cx, c, r);
             end_row(r);
+            ++rows_done;
         }
     } else {
-        for (uint32_t n = cy; n < nrows_cta; n += p.ty) {
+        for (uint32_t n = cy;; n += p.ty) {
             Row r; begin_row(n, r);
+            if (r.end) break;
+            ++rows_done;
             for (uint32_t q = cx; q < Q; q += p.tx) {
                 Cols c{};
                 load_cols(q, c);
@@ -785,7 +878,7 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
     }
     __syncwarp();                                // done: nothing this warp could still read
     if (lane == 0) { __threadfence_block(); progress[tid >> 5] = 0xffffffffu; }
-    if (p.trace.buf && tid == 0) { t_trace[1] = gtimer(); trace_put(p.trace, 1u, blockIdx.x, nrows_cta, t_trace, 2); }
+    if (p.trace.buf && tid == 0) { t_trace[1] = gtimer(); trace_put(p.trace, 1u, blockIdx.x, rows_done, t_trace, 2); }
     finish();
 }
 
@@ -1057,6 +1150,33 @@ tk_error_code_t tkb::preprocess_batch_impl(const tk_b200_preprocess_batch_params
     if (total_rows / grid.x >= 0x7fffffffull) {                               // the kernel counts a CTA's rows in 32 bits
         tk_error_set_detail("%llu output rows are more than one launch takes", total_rows);
         return TK_ERROR_NOT_IMPLEMENTED;
+    }
+
+    // Static / dynamic split (PreK): the dynamic part only when a CTA has enough rows for it to matter.
+    // TK_B200_PRE_DYN="<percent handed out dynamically>,<rows per chunk>" (experiments; "0" = all static).
+    struct DynCfg { uint32_t pct, rows; };
+    static const DynCfg dyn = [] {
+        DynCfg c{30, 4};
+        if (const char* e = getenv("TK_B200_PRE_DYN")) {
+            unsigned a = 0, b = 0;
+            const int got = sscanf(e, "%u,%u", &a, &b);
+            if (got >= 1) c.pct = a > 100 ? 100 : a;
+            if (got >= 2 && b >= 1 && b <= 64) c.rows = b;
+        }
+        return c;
+    }();
+    k.static_rows = total_rows; k.dyn_rows = 0; k.dyn_chunks = 0; k.dyn_slot = 0;
+    if (dyn.pct && total_rows / grid.x >= 32) {
+        const uint32_t cr = dyn.rows * rows_in_flight;                       // chunk: dyn.rows rows per consumer row group
+        unsigned long long dyn_total = total_rows * dyn.pct / 100;
+        unsigned long long chunks = dyn_total / cr;
+        if (chunks > 0x7fffffffull) chunks = 0x7fffffffull;
+        if (chunks) {
+            static std::atomic<uint32_t> next_slot{0};
+            k.dyn_rows = cr; k.dyn_chunks = (uint32_t)chunks;
+            k.static_rows = total_rows - chunks * cr;
+            k.dyn_slot = next_slot.fetch_add(1, std::memory_order_relaxed) % kPreSlots;
+        }
     }
 
     const bool f16 = prm->output_type == TK_B200_OUT_F16;
