@@ -320,3 +320,67 @@ def test_host_entry_point_threads_do_not_leak_device_memory():
     free2, _ = torch.cuda.mem_get_info()
     assert free2 >= free1 + (8 << 20)                     # this thread's ~11 MB of scratch went back
     assert np.array_equal(bits(V.preprocessor_resize_and_normalize_to_chw(fr, 640, 640)), bits(ref))   # and it comes back on demand
+
+
+_DYN_CHILD = r"""
+import sys
+import numpy as np, torch
+sys.path.insert(0, "tests"); sys.path.insert(0, ".")
+import synth
+from oracle import oracle as O
+from trackiellm_b200 import vision as V
+bits = lambda a: np.ascontiguousarray(a, np.float32).view(np.uint32)
+for (w, h, ow, oh, n, fmt) in ((320, 200, 256, 192, 40, "rgb"), (1920, 1080, 640, 640, 24, "rgb"), (3840, 2160, 640, 640, 10, "i420")):
+    if fmt == "i420":
+        fr = np.stack([synth.i420_frame(w, h, 300 + i) for i in range(n)])
+        kw = dict(width=w, height=h, fmt=V.PIXEL_I420)
+        ref = lambda i: O.preprocess_rgb8(O.i420_to_rgb8(fr[i], w, h), ow, oh)
+    else:
+        fr = np.stack([synth.rgb_frame(w, h, 300 + i) for i in range(n)])
+        kw = {}
+        ref = lambda i: O.preprocess_rgb8(fr[i], ow, oh)
+    d = torch.from_numpy(fr).cuda()
+    outs = [V.preprocess_batch(d, ow, oh, **kw).cpu().numpy() for _ in range(4)]
+    for o in outs[1:]:
+        assert np.array_equal(bits(o), bits(outs[0])), "launches differ"
+    for i in (0, n // 3, n - 1):
+        assert np.array_equal(bits(outs[0][i]), bits(ref(i))), (w, h, i)
+print("DYN-OK")
+"""
+
+
+@pytest.mark.parametrize("dyn", ["0", "100,1", "100,4", "55,3"])
+def test_dynamic_row_share_extremes_bitexact(dyn):
+    """The pre-process kernel hands part of the output rows out dynamically (PreK::static_rows, TK_B200_PRE_DYN).  The
+    split is read once per process, so each setting runs in a child: all static, ALL rows dynamic in one-row and in
+    four-row chunks (every chunk restarts the producer's cursors; every row pair straddles two chunks), and an odd
+    split — dense (1080p), upscaling-ish small frames and sparse I420 staging — bit-exact against the oracle and
+    identical from launch to launch."""
+    import subprocess
+    import sys
+    env = dict(os.environ, TK_B200_PRE_DYN=dyn)
+    r = subprocess.run([sys.executable, "-c", _DYN_CHILD], env=env, capture_output=True, text=True, timeout=600,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0 and "DYN-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_concurrent_launches_on_two_streams_take_different_chunk_counters():
+    """Launches in flight at once each take their own chunk counter (g_pre_work[slot]): two streams, many launches,
+    results identical to the serial ones."""
+    n, w, h = 24, 1280, 720
+    fa = torch.from_numpy(np.stack([synth.rgb_frame(w, h, 500 + i) for i in range(n)])).cuda()
+    fb = torch.from_numpy(np.stack([synth.rgb_frame(w, h, 600 + i) for i in range(n)])).cuda()
+    want_a = V.preprocess_batch(fa, 640, 640).clone()
+    want_b = V.preprocess_batch(fb, 640, 640).clone()
+    torch.cuda.synchronize()
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    oa = [torch.empty_like(want_a) for _ in range(6)]
+    ob = [torch.empty_like(want_b) for _ in range(6)]
+    for i in range(6):
+        with torch.cuda.stream(sa):
+            V.preprocess_batch(fa, 640, 640, out=oa[i])
+        with torch.cuda.stream(sb):
+            V.preprocess_batch(fb, 640, 640, out=ob[i])
+    torch.cuda.synchronize()
+    for i in range(6):
+        assert torch.equal(oa[i], want_a) and torch.equal(ob[i], want_b)
