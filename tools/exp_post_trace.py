@@ -68,5 +68,14 @@ for rep in range(3):
         rel = (tk - t0) / 1e3
         print(f"{name}: {m.sum()}  start {rel[:, 0].min():.1f}..{rel[:, 0].max():.1f} us, end {rel[:, 5].min():.1f}..{rel[:, 5].max():.1f} us (median {np.median(rel[:, 5]):.1f})")
         ph = np.diff(rel, axis=1)
+        if k == 3 and not FUSED:
+            # scan end per CTA, grouped by cluster (8 consecutive CTAs = one frame): is the spread inside clusters or between them?
+            blk = (rec[m][:, 0] & np.uint64(0xffffffff)).astype(np.int64)
+            order = np.argsort(blk)
+            se = rel[order, 1].reshape(-1, 8)
+            print(f"   scan end: all CTAs min {se.min():.1f} / median {np.median(se):.1f} / max {se.max():.1f}; per cluster: mean of (max - min) {np.mean(se.max(1) - se.min(1)):.2f} us, "
+                  f"cluster means min {se.mean(1).min():.1f} / max {se.mean(1).max():.1f}, cluster max: min {se.max(1).min():.1f} / median {np.median(se.max(1)):.1f} / max {se.max(1).max():.1f}")
+            smid = (rec[m][:, 1] >> np.uint64(32)).astype(np.int64)[order].reshape(-1, 8)
+            print(f"   SMs of cluster 0: {smid[0].tolist()}, rank-wise mean scan end: {np.round(se.mean(0), 1).tolist()}")
         for j, nm in enumerate(phases):
             print(f"   {nm:26s}: median {np.median(ph[:, j]):6.2f} us  p90 {np.percentile(ph[:, j], 90):6.2f}  max {ph[:, j].max():6.2f}   (phase ends at median {np.median(rel[:, j + 1]):6.1f} us)")
