@@ -118,7 +118,12 @@ __device__ __forceinline__ void col_consts(const PreK& p, int xb, int& off, uint
 
 // Fetch the 2x2 source neighbourhood of one output pixel as biased floats
 // m[k][c] = 2^23 + value, k = {top-left, top-right, bottom-left, bottom-right}.
-template <int FMT>
+// XU (RGB8, EXACT): the bytes per source row that sit in byte 2 / byte 3 of a word after the funnel shifts — B of the
+// left pixel, R, G, B of the right one — are converted by the conversion unit (I2F.U8 with a byte selector, no ALU-pipe
+// instruction) and arrive as PLAIN floats p, not 2^23 + p: the kernel is bound by what it issues to the ALU pipe
+// (profiles/r2_experiments.md §9), the conversion unit is idle.  blend_norm2 multiplies those taps directly.  Four of
+// the six bytes is the balance: 94.8 -> 92.5 us with two, 90.4 us with four, 106 us with all six (the unit saturates).
+template <int FMT, bool XU = false>
 __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, const uint8_t* row1,
                                            int off, uint32_t aux, float (&m)[4][3]) {
     if constexpr (FMT == FMT_RGB8) {
@@ -129,10 +134,21 @@ __device__ __forceinline__ void fetch_quad(const PreK& p, const uint8_t* row0, c
         const uint32_t sh = aux;                         // 0, 8, 16, 24
         uint32_t alo = __funnelshift_r(a0, a1, sh), ahi = __funnelshift_r(a1, a2, sh);
         uint32_t blo = __funnelshift_r(b0, b1, sh), bhi = __funnelshift_r(b1, b2, sh);
-        m[0][0] = magic_byte(alo, 0); m[0][1] = magic_byte(alo, 1); m[0][2] = magic_byte(alo, 2);
-        m[1][0] = magic_byte(alo, 3); m[1][1] = magic_byte(ahi, 0); m[1][2] = magic_byte(ahi, 1);
-        m[2][0] = magic_byte(blo, 0); m[2][1] = magic_byte(blo, 1); m[2][2] = magic_byte(blo, 2);
-        m[3][0] = magic_byte(blo, 3); m[3][1] = magic_byte(bhi, 0); m[3][2] = magic_byte(bhi, 1);
+        m[0][0] = magic_byte(alo, 0); m[0][1] = magic_byte(alo, 1);
+        m[2][0] = magic_byte(blo, 0); m[2][1] = magic_byte(blo, 1);
+        if constexpr (XU) {
+            // window bytes 2..5 in one more word: G and B of the right pixel land in its bytes 2 and 3 as well
+            const uint32_t amid = __funnelshift_r(alo, ahi, 16), bmid = __funnelshift_r(blo, bhi, 16);
+            m[0][2] = (float)((alo >> 16) & 0xffu); m[1][0] = (float)(alo >> 24);
+            m[1][1] = (float)((amid >> 16) & 0xffu); m[1][2] = (float)(amid >> 24);
+            m[2][2] = (float)((blo >> 16) & 0xffu); m[3][0] = (float)(blo >> 24);
+            m[3][1] = (float)((bmid >> 16) & 0xffu); m[3][2] = (float)(bmid >> 24);
+        } else {
+            m[0][2] = magic_byte(alo, 2); m[1][0] = magic_byte(alo, 3);
+            m[1][1] = magic_byte(ahi, 0); m[1][2] = magic_byte(ahi, 1);
+            m[2][2] = magic_byte(blo, 2); m[3][0] = magic_byte(blo, 3);
+            m[3][1] = magic_byte(bhi, 0); m[3][2] = magic_byte(bhi, 1);
+        }
     } else if constexpr (FMT == FMT_RGBA8) {
         const uint32_t* a = reinterpret_cast<const uint32_t*>(row0 + off);
         const uint32_t* b = reinterpret_cast<const uint32_t*>(row1 + off);
@@ -199,15 +215,17 @@ __device__ __forceinline__ float blend_norm(const PreK& p, int c, float m1, floa
 // fma(m, w, -2^23*w): -2^23*w is exact (a power-of-two scaling), so the fma computes m*w - 2^23*w = p*w exactly and
 // rounds ONCE — the same value as fmul(p, w) — and the four subtractions that would turn m back into p disappear.
 // cxd = -2^23*xd, comx = -2^23*(1-xd).
+// plain_l / plain_r: the left (m1, m3) / right (m2, m4) taps are plain byte values (fetch_quad<.., XU>): p * w directly.
 template <bool EXACT>
 __device__ __forceinline__ float2 blend_norm2(const PreK& p, int c, float2 m1, float2 m2, float2 m3, float2 m4,
-                                              float2 xd, float2 omx, float2 cxd, float2 comx, float yd, float omy) {
+                                              float2 xd, float2 omx, float2 cxd, float2 comx, float yd, float omy,
+                                              bool plain_l = false, bool plain_r = false) {
     if constexpr (EXACT) {
         const float2 yd2 = f2s(yd), omy2 = f2s(omy);
-        const float2 t1 = mul2(fma2(m1, omx, comx), omy2);
-        const float2 t2 = mul2(fma2(m2, xd, cxd), omy2);
-        const float2 t3 = mul2(fma2(m3, omx, comx), yd2);
-        const float2 t4 = mul2(fma2(m4, xd, cxd), yd2);
+        const float2 t1 = mul2(plain_l ? mul2(m1, omx) : fma2(m1, omx, comx), omy2);
+        const float2 t2 = mul2(plain_r ? mul2(m2, xd) : fma2(m2, xd, cxd), omy2);
+        const float2 t3 = mul2(plain_l ? mul2(m3, omx) : fma2(m3, omx, comx), yd2);
+        const float2 t4 = mul2(plain_r ? mul2(m4, xd) : fma2(m4, xd, cxd), yd2);
         const float2 v = sum2(sum2(sum2(t1, t2, p.one), t3, p.one), t4, p.one);
         const float2 t = sum2(mul2(v, f2s(1.0f / 255.0f)), f2s(-p.mean[c]), p.one);        // x - mean == x + (-mean)
         const float2 q = mul2(t, f2s(p.rstd[c]));
@@ -309,6 +327,10 @@ __device__ __forceinline__ __half2 lerp_pair_half(uint32_t tl, uint32_t tr, uint
 }
 
 enum { AR_EXACT = 0, AR_FAST = 1, AR_HALF = 2 };
+#ifndef TK_PRE_XU
+#define TK_PRE_XU 1
+#endif
+static constexpr bool kPreXu = TK_PRE_XU != 0;   // byte -> float of four taps per pixel on the conversion unit (fetch_quad)
 
 #ifdef TK_B200_CHECKED
 // The ring slot the consumer is about to read / has just read must hold exactly source row `row` of the frame.
@@ -803,13 +825,15 @@ __global__ void __launch_bounds__(384, 2) preprocess_kernel(const PreK p) {
 #pragma unroll
                 for (int j = 0; j < 4; j += 2) {                 // two neighbouring pixels per packed-fp32 pass
                     float ma[4][3], mb[4][3];
-                    fetch_quad<FMT>(p, r.row0, r.row1, c.off[j], c.aux[j], ma);
-                    fetch_quad<FMT>(p, r.row0, r.row1, c.off[j + 1], c.aux[j + 1], mb);
+                    constexpr bool XU = kPreXu && EXACT && FMT == FMT_RGB8;
+                    fetch_quad<FMT, XU>(p, r.row0, r.row1, c.off[j], c.aux[j], ma);
+                    fetch_quad<FMT, XU>(p, r.row0, r.row1, c.off[j + 1], c.aux[j + 1], mb);
 #pragma unroll
                     for (int ch = 0; ch < 3; ++ch) {
                         const float2 v = blend_norm2<EXACT>(p, ch, f2(ma[0][ch], mb[0][ch]), f2(ma[1][ch], mb[1][ch]),
                                                             f2(ma[2][ch], mb[2][ch]), f2(ma[3][ch], mb[3][ch]), c.xd2[j >> 1],
-                                                            c.omx2[j >> 1], c.cxd2[j >> 1], c.comx2[j >> 1], r.yd, r.omy);
+                                                            c.omx2[j >> 1], c.cxd2[j >> 1], c.comx2[j >> 1], r.yd, r.omy,
+                                                            XU && ch == 2, XU);
                         o[ch][j] = (LBOX && ((c.padmask >> j) & 1u)) ? padn[ch] : v.x;
                         o[ch][j + 1] = (LBOX && ((c.padmask >> (j + 1)) & 1u)) ? padn[ch] : v.y;
                     }
