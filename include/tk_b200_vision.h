@@ -132,6 +132,10 @@ typedef struct {
     TkFloat3           std_dev;
 } tk_b200_preprocess_batch_params_t;
 
+/* Asynchronous on `stream`.  Large launches hand part of their output rows out dynamically from a chunk counter in the
+ * library's device memory; every call takes the next of 64 counters, so up to 64 launches may be in flight on a device
+ * at once.  A launch recorded into a CUDA graph keeps the counter it was captured with: replays of ONE graph must not
+ * overlap each other on the GPU (replay it on one stream, or capture it once per stream). */
 TK_NODISCARD tk_error_code_t tk_b200_preprocess_batch(const tk_b200_preprocess_batch_params_t* params, cudaStream_t stream);
 
 /* One decoded proposal / detection (28 bytes, packed ints and one float). */
