@@ -368,7 +368,7 @@ __device__ __noinline__ void check_ring_row(const PreK& p, const uint8_t* base, 
 static constexpr uint32_t kRecs = 32;
 static constexpr uint32_t kSmemRecs = 512;                        // 32 x 32 B
 static constexpr uint32_t kSmemQ0 = kSmemRecs + kRecs * 32;       // [kRecs] u32: first ring sequence number row n needs (producer only)
-static constexpr uint32_t kSmemChk = kSmemQ0 + kRecs * 4;         // CHECKED build: [kRecs] {frame, source row, n}
+[[maybe_unused]] static constexpr uint32_t kSmemChk = kSmemQ0 + kRecs * 4;   // CHECKED build: [kRecs] {frame, source row, n}
 static constexpr uint32_t kSmemRq = 2048;                         // [8] {first, end} global output rows of the work ranges in flight (producer only)
 static constexpr uint32_t kSmemTabs = 2176;                       // column tables
 
